@@ -1,0 +1,62 @@
+"""Pin the CPU oracle against fixtures produced by the reference's own code (tests/golden)."""
+import numpy as np
+import pytest
+import torch
+
+import enarf_oracle as O
+import golden_util as G
+
+
+def rel(a, b):
+    a, b = torch.as_tensor(a).double(), torch.as_tensor(b).double()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize("name", G.CASES)
+def test_end_to_end_matches_reference(name):
+    """Same RNG draws as the reference -> colour / mask / disparity within 1e-4 relative."""
+    g, cfg, inp, tp, layers, z_rend = G.load(name)
+    sc = G.scene(cfg, inp, tp, layers, z_rend)
+    img = O.whole_image_grid(cfg["size"], cfg["size"], cfg["B"])
+    rng = {"mode": "given", "idx": torch.from_numpy(g["idx"].astype(np.int64)), "jitter": torch.from_numpy(g["jitter"])}
+    with torch.no_grad():
+        out = O.render(sc, img, cfg["Nc"], cfg["Nf"], rng)
+    s = cfg["size"]
+    # the B>1 reference path is itself only ~1e-3 accurate (side-by-side plane trick)
+    tol = 1e-4 if cfg["B"] == 1 else 3e-3
+    assert out["fine_weights"].shape[1] == int(g["n_rays"])
+    composed = out["color"] + (1 - out["mask"][:, None]) * -1.0          # generator.py:105-107, black bg
+    assert rel(composed.reshape(cfg["B"], 3, s, s), g["color"]) < tol
+    assert rel(out["mask"].reshape(cfg["B"], s, s), g["mask"]) < tol
+    assert rel(out["disparity"] * 3.0, g["disparity"].reshape(cfg["B"], -1)) < tol
+    if "fine_weights" in g:
+        assert rel(out["fine_weights"], g["fine_weights"]) < tol
+        assert rel(out["fine_depth"], g["fine_depth"]) < 1e-5
+        assert rel(out["coarse_weights_blurred"], g["coarse_weights_blurred"]) < tol
+        assert rel(out["coarse_density"], g["coarse_density"]) < tol
+
+
+@pytest.mark.parametrize("name", ["b1_s32", "b2_s24", "b1_s32_center_fixed"])
+def test_part_masks_bit_exact_on_reference_points(name):
+    """Part-selection masks: feed the reference's own fine points; every (sample,part,point) bit
+    must equal the reference's in_cube & |canon|<1 mask."""
+    g, cfg, inp, tp, layers, z_rend = G.load(name)
+    sc = G.scene(cfg, inp, tp, layers, z_rend)
+    pts = torch.from_numpy(g["fine_points"])
+    _, _, valid = O.part_transform(pts, sc.pose, sc.cscale, sc.canonical_pose)
+    shape = tuple(int(v) for v in g["fine_valid_shape"])
+    ref = np.unpackbits(g["fine_valid_bits"])[:int(np.prod(shape))].reshape(shape).astype(bool)
+    flips = int((valid.numpy() != ref).sum())
+    assert flips == 0, f"{flips} of {ref.size} mask bits differ"
+
+
+def test_fp64_oracle_agrees_with_fp32():
+    g, cfg, inp, tp, layers, z_rend = G.load("b1_s32")
+    img = O.whole_image_grid(cfg["size"], cfg["size"], cfg["B"])
+    rng = {"mode": "given", "idx": torch.from_numpy(g["idx"].astype(np.int64)), "jitter": torch.from_numpy(g["jitter"])}
+    with torch.no_grad():
+        o32 = O.render(G.scene(cfg, inp, tp, layers, z_rend), img, cfg["Nc"], cfg["Nf"], rng)
+        o64 = O.render(G.scene(cfg, inp, tp, layers, z_rend, torch.float64), img, cfg["Nc"], cfg["Nf"], rng)
+    if o32["fine_weights"].shape == o64["fine_weights"].shape:
+        assert rel(o32["color"], o64["color"]) < 1e-4
+        assert rel(o32["mask"], o64["mask"]) < 1e-4
