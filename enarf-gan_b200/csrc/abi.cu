@@ -1,0 +1,45 @@
+// Error plumbing and argument checks of the C ABI (include/enarf_b200.h).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+static thread_local char g_err[512] = "";
+
+void enarf_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" const char* enarf_last_error(void) { return g_err; }
+extern "C" int enarf_version(void) { return 100; }
+
+int enarf_sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+int enarf_check_scene(const enarf_scene_t* sc, const char* who) {
+    ENARF_REQUIRE(sc != nullptr, ENARF_ERR_INVALID_ARG, "%s: scene is NULL", who);
+    ENARF_REQUIRE(sc->B > 0 && sc->P > 0 && sc->H > 1 && sc->W > 1, ENARF_ERR_INVALID_ARG,
+                  "%s: bad scene sizes B=%d P=%d H=%d W=%d", who, sc->B, sc->P, sc->H, sc->W);
+    ENARF_REQUIRE(sc->P <= ENARF_MAX_PARTS, ENARF_ERR_UNSUPPORTED, "%s: P=%d exceeds %d parts", who, sc->P,
+                  ENARF_MAX_PARTS);
+    ENARF_REQUIRE(sc->pose && sc->cscale && sc->canon_pose, ENARF_ERR_INVALID_ARG, "%s: NULL pose buffers", who);
+    ENARF_REQUIRE(sc->feat_planes && sc->prob_planes, ENARF_ERR_INVALID_ARG, "%s: NULL plane buffers", who);
+    ENARF_REQUIRE(sc->feat_dtype == ENARF_DTYPE_F32 || sc->feat_dtype == ENARF_DTYPE_BF16, ENARF_ERR_INVALID_ARG,
+                  "%s: bad feat_dtype %d", who, sc->feat_dtype);
+    ENARF_REQUIRE(((uintptr_t)sc->feat_planes & 15) == 0, ENARF_ERR_INVALID_ARG,
+                  "%s: feat_planes must be 16-byte aligned", who);
+    ENARF_REQUIRE(sc->w1 && sc->w2 && sc->w3 && sc->b1 && sc->b2 && sc->b3, ENARF_ERR_INVALID_ARG,
+                  "%s: NULL decoder buffers", who);
+    return ENARF_OK;
+}

@@ -1,0 +1,141 @@
+// Shared device/host helpers for libenarf_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/enarf_b200.h"
+
+#define FEAT ENARF_FEAT_DIM
+#define HID ENARF_HIDDEN
+#define N_PROBE 32  // depth probes per ray (reference: libraries/NeRF/rendering.py:18)
+
+// ---- host side: thread-local error string, argument / launch checks ---------------------------
+void enarf_set_error(const char* fmt, ...);
+
+#define ENARF_REQUIRE(cond, code, ...)   \
+    do {                                 \
+        if (!(cond)) {                   \
+            enarf_set_error(__VA_ARGS__); \
+            return (code);               \
+        }                                \
+    } while (0)
+
+#define ENARF_CHECK_LAUNCH(name)                                                     \
+    do {                                                                             \
+        cudaError_t e__ = cudaGetLastError();                                        \
+        if (e__ != cudaSuccess) {                                                    \
+            enarf_set_error("%s: CUDA error: %s", (name), cudaGetErrorString(e__)); \
+            return ENARF_ERR_CUDA;                                                   \
+        }                                                                            \
+    } while (0)
+
+int enarf_check_scene(const enarf_scene_t* sc, const char* who);
+int enarf_sm_count();
+
+// ---- contract arithmetic: every product / sum rounded separately, never contracted ------------
+// (oracle/enarf_oracle.py "ARITHMETIC CONTRACT"; these feed the bit-exact masks and indices)
+__device__ __forceinline__ float cmul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float cadd(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float csub(float a, float b) { return __fsub_rn(a, b); }
+// a*(1-t) + b*t                      (rendering.py:126-129,198-200)
+__device__ __forceinline__ float clerp(float a, float b, float t) {
+    return cadd(cmul(a, csub(1.0f, t)), cmul(b, t));
+}
+// (m0*v0 + m1*v1) + m2*v2
+__device__ __forceinline__ float cdot3(float m0, float m1, float m2, float v0, float v1, float v2) {
+    return cadd(cadd(cmul(m0, v0), cmul(m1, v1)), cmul(m2, v2));
+}
+
+// Part frames staged in shared memory: per part 28 floats.
+//   [0..8]  R (row-major 3x3 of the part->camera frame)    [9..11] t
+//   [12]    canonical scale                                 [13..21] Rc   [22..24] tc
+#define PART_STRIDE 28
+
+__device__ __forceinline__ void load_part_params(float* s_part, const enarf_scene_t& sc, int b, int tid, int nthreads) {
+    for (int i = tid; i < sc.P * PART_STRIDE; i += nthreads) {
+        int p = i / PART_STRIDE, j = i - p * PART_STRIDE;
+        float v = 0.f;
+        if (j < 12) {
+            int r = (j < 9) ? j / 3 : j - 9, c = (j < 9) ? j % 3 : 3;
+            v = sc.pose[((size_t)(b * sc.P + p) * 4 + r) * 4 + c];
+        } else if (j == 12) {
+            v = sc.cscale[b * sc.P + p];
+        } else if (j < 25) {
+            int jj = j - 13;
+            int r = (jj < 9) ? jj / 3 : jj - 9, c = (jj < 9) ? jj % 3 : 3;
+            v = sc.canon_pose[((size_t)p * 4 + r) * 4 + c];
+        }
+        s_part[i] = v;
+    }
+}
+
+// local = R^T (x - t); |local| <= 1 on every axis           (models/narf.py:158-162, NeRF/utils.py:39-43)
+__device__ __forceinline__ bool part_local(const float* q, float x, float y, float z, float& l0, float& l1, float& l2) {
+    float d0 = csub(x, q[9]), d1 = csub(y, q[10]), d2 = csub(z, q[11]);
+    l0 = cdot3(q[0], q[3], q[6], d0, d1, d2);
+    l1 = cdot3(q[1], q[4], q[7], d0, d1, d2);
+    l2 = cdot3(q[2], q[5], q[8], d0, d1, d2);
+    return fabsf(l0) <= 1.f && fabsf(l1) <= 1.f && fabsf(l2) <= 1.f;
+}
+
+// canon = Rc (local * scale) + tc; valid iff in-cube and |canon| < 1 on every axis (narf.py:165-169,200-201)
+__device__ __forceinline__ bool part_canonical(const float* q, float x, float y, float z, float& c0, float& c1, float& c2) {
+    float l0, l1, l2;
+    bool in = part_local(q, x, y, z, l0, l1, l2);
+    float s0 = cmul(l0, q[12]), s1 = cmul(l1, q[12]), s2 = cmul(l2, q[12]);
+    c0 = cadd(cdot3(q[13], q[14], q[15], s0, s1, s2), q[22]);
+    c1 = cadd(cdot3(q[16], q[17], q[18], s0, s1, s2), q[23]);
+    c2 = cadd(cdot3(q[19], q[20], q[21], s0, s1, s2), q[24]);
+    return in && fabsf(c0) < 1.f && fabsf(c1) < 1.f && fabsf(c2) < 1.f;
+}
+
+// Bilinear footprint, zeros padding, align_corners=False (TriplaneSampler_kernel.cu:40-74 semantics).
+struct Bilin {
+    int x0, y0;          // top-left texel (may be -1)
+    float w00, w01, w10, w11;  // weights of (y0,x0) (y0,x0+1) (y0+1,x0) (y0+1,x0+1), zero when out of range
+};
+
+__device__ __forceinline__ Bilin bilin_setup(float x, float y, int W, int H) {
+    float ix = ((x + 1.f) * W - 1.f) * 0.5f;
+    float iy = ((y + 1.f) * H - 1.f) * 0.5f;
+    float fx = floorf(ix), fy = floorf(iy);
+    Bilin b;
+    b.x0 = (int)fx;
+    b.y0 = (int)fy;
+    float ax = ix - fx, ay = iy - fy;
+    bool xl = b.x0 >= 0 && b.x0 < W, xr = b.x0 + 1 >= 0 && b.x0 + 1 < W;
+    bool yt = b.y0 >= 0 && b.y0 < H, yb = b.y0 + 1 >= 0 && b.y0 + 1 < H;
+    b.w00 = (xl && yt) ? (1.f - ax) * (1.f - ay) : 0.f;
+    b.w01 = (xr && yt) ? ax * (1.f - ay) : 0.f;
+    b.w10 = (xl && yb) ? (1.f - ax) * ay : 0.f;
+    b.w11 = (xr && yb) ? ax * ay : 0.f;
+    return b;
+}
+
+// scalar (1-channel) bilinear fetch from a row-major H x W plane
+__device__ __forceinline__ float bilin_fetch1(const float* __restrict__ plane, const Bilin& b, int W) {
+    float v = 0.f;
+    const float* r0 = plane + (ptrdiff_t)b.y0 * W + b.x0;
+    if (b.w00 != 0.f) v = fmaf(b.w00, __ldg(r0), v);
+    if (b.w01 != 0.f) v = fmaf(b.w01, __ldg(r0 + 1), v);
+    if (b.w10 != 0.f) v = fmaf(b.w10, __ldg(r0 + W), v);
+    if (b.w11 != 0.f) v = fmaf(b.w11, __ldg(r0 + W + 1), v);
+    return v;
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+
+// ---- Philox4x32-10 (Salmon et al. 2011); oracle twin: enarf_oracle.philox4x32 ------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        uint32_t h0 = __umulhi(0xD2511F53u, c.x), l0 = 0xD2511F53u * c.x;
+        uint32_t h1 = __umulhi(0xCD9E8D57u, c.z), l1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(h1 ^ c.y ^ k.x, l1, h0 ^ c.w ^ k.y, l0);
+        k.x += 0x9E3779B9u;
+        k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+__device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }

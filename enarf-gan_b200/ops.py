@@ -1,0 +1,199 @@
+"""Torch-facing operators over the C ABI: one function per exported entry point plus the autograd
+Function of the fused fine pass.  Tensors in, tensors out; every buffer is allocated here by torch's
+caching allocator and handed to the library as a raw pointer on torch's current stream."""
+import ctypes
+
+import torch
+
+from . import _abi
+from ._abi import check, lib, ptr, stream_ptr
+
+FEAT_DIM = 32
+HIDDEN = 64
+
+
+class SceneBuffers:
+    """Owns the device tensors one render call needs and the enarf_scene_t that points at them.
+
+    pose (B,P,4,4) is the part frames with scaled translation (rendering.py:258-260 applied), cscale
+    (B,P) = canonical_bone_length / bone_length / coordinate_scale (narf.py:165), canon_pose (P,4,4),
+    tri_plane (B,(32+P)*3,H,W) NCHW as the reference produces it, decoder = [(W_eff (B,out,in), bias), ...].
+    """
+
+    def __init__(self, pose, cscale, canon_pose, tri_plane, decoder, plane_dtype=torch.float32, feat_planes=None):
+        B, P = pose.shape[:2]
+        H, W = tri_plane.shape[-2:]
+        assert tri_plane.shape[1] == (FEAT_DIM + P) * 3, "tri-plane must have (32+P)*3 channels"
+        f32 = lambda t: t.detach().to(torch.float32).contiguous()
+        self.pose, self.cscale, self.canon_pose = f32(pose), f32(cscale), f32(canon_pose)
+        self.tri_plane = tri_plane if (tri_plane.dtype == torch.float32 and tri_plane.is_contiguous()) \
+            else tri_plane.detach().to(torch.float32).contiguous()
+        self.plane_dtype = plane_dtype
+        self.B, self.P, self.H, self.W = B, P, H, W
+        (w1, b1), (w2, b2), (w3, b3) = decoder
+        assert w1.shape[1:] == (HIDDEN, FEAT_DIM) and w2.shape[1:] == (HIDDEN, HIDDEN) and w3.shape[1:] == (4, HIDDEN)
+        self.w = [f32(w1), f32(w2), f32(w3)]
+        self.b = [f32(b1).reshape(-1), f32(b2).reshape(-1), f32(b3).reshape(-1)]
+        if feat_planes is None:
+            feat_planes = repack_planes(self.tri_plane.detach(), plane_dtype)
+        self.feat_planes = feat_planes
+        self.prob_view = self.tri_plane.detach()[:, FEAT_DIM * 3:]
+        s = _abi.Scene()
+        s.B, s.P, s.H, s.W = B, P, H, W
+        s.pose, s.cscale, s.canon_pose = ptr(self.pose), ptr(self.cscale), ptr(self.canon_pose)
+        s.feat_planes = ptr(self.feat_planes, None)
+        s.feat_dtype = _abi.DTYPE_F32 if plane_dtype == torch.float32 else _abi.DTYPE_BF16
+        s.prob_planes = self.prob_view.data_ptr()
+        s.prob_batch_stride = self.tri_plane.stride(0)
+        s.w1, s.w2, s.w3 = (ptr(t) for t in self.w)
+        s.b1, s.b2, s.b3 = (ptr(t) for t in self.b)
+        self.c = s
+
+    @property
+    def ref(self):
+        return ctypes.byref(self.c)
+
+
+def repack_planes(tri_plane, dtype=torch.float32):
+    """(B,C,H,W) fp32 NCHW -> channels-last feature planes (B,3,H,W,32)."""
+    B, C, H, W = tri_plane.shape
+    out = torch.empty(B, 3, H, W, FEAT_DIM, device=tri_plane.device, dtype=dtype)
+    code = _abi.DTYPE_F32 if dtype == torch.float32 else _abi.DTYPE_BF16
+    check(lib().enarf_repack_planes(ptr(tri_plane), B, C, H, W, ptr(out, None), code, stream_ptr()))
+    return out
+
+
+def unpack_plane_grads(d_feat, d_tri_plane):
+    """Adds d_feat (B,3,H,W,32) into channels [0,96) of the NCHW gradient d_tri_plane."""
+    B, C, H, W = d_tri_plane.shape
+    check(lib().enarf_unpack_plane_grads(ptr(d_feat), B, C, H, W, ptr(d_tri_plane), stream_ptr()))
+    return d_tri_plane
+
+
+def near_far(pose, near0=0.3, far0=5.0):
+    """Batch-global near/far as a 2-element device tensor (no host sync)."""
+    B, P = pose.shape[:2]
+    out = torch.empty(2, device=pose.device, dtype=torch.float32)
+    check(lib().enarf_near_far(ptr(pose), B, P, near0, far0, ptr(out), stream_ptr()))
+    return out
+
+
+def depth_range(image_coord, inv_K, pose, nearfar=None):
+    """image_coord (B,3,n), inv_K (B,3,3), pose (B,P,4,4) -> dmin, dmax (B,n), dir (B,3,n), validity (B,n) bool."""
+    B, _, n = image_coord.shape
+    P = pose.shape[1]
+    if nearfar is None:
+        nearfar = near_far(pose)
+    dev = pose.device
+    dmin = torch.empty(B, n, device=dev)
+    dmax = torch.empty(B, n, device=dev)
+    direction = torch.empty(B, 3, n, device=dev)
+    valid = torch.empty(B, n, device=dev, dtype=torch.uint8)
+    check(lib().enarf_depth_range(ptr(image_coord), ptr(inv_K), ptr(pose), ptr(nearfar), B, P, n, ptr(dmin), ptr(dmax),
+                                  ptr(direction), ptr(valid, torch.uint8), stream_ptr()))
+    return dmin, dmax, direction, valid.bool()
+
+
+def render_coarse(scene, dmin, dmax, direction, Nc, want_density=False):
+    """-> blurred coarse weights (B,n,Nc) [, density (B,n,Nc)]."""
+    B, n = dmin.shape
+    wb = torch.empty(B, n, Nc, device=dmin.device)
+    den = torch.empty(B, n, Nc, device=dmin.device) if want_density else None
+    check(lib().enarf_render_coarse(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), n, Nc, ptr(wb),
+                                    ptr(den, allow_none=True), stream_ptr()))
+    return (wb, den) if want_density else wb
+
+
+def fine_sample(weights, Nf, idx=None, jitter=None, seed=0, ray_id_offset=0, want_idx=False):
+    """weights (...,Nc) -> sorted bins (...,Nf).  idx+jitter given -> parity mode, else Philox."""
+    Nc = weights.shape[-1]
+    R = weights.numel() // Nc
+    bins = torch.empty(*weights.shape[:-1], Nf, device=weights.device)
+    idx_out = torch.empty(*weights.shape[:-1], Nf, device=weights.device, dtype=torch.int32) if want_idx else None
+    if idx is not None:
+        idx = idx.to(torch.int32).contiguous()
+        jitter = jitter.to(torch.float32).contiguous()
+        mode = _abi.RNG_GIVEN
+    else:
+        mode = _abi.RNG_PHILOX
+    check(lib().enarf_fine_sample(ptr(weights), R, Nc, Nf, mode, ptr(idx, torch.int32, True), ptr(jitter, allow_none=True),
+                                  seed, ray_id_offset, ptr(bins), ptr(idx_out, torch.int32, True), stream_ptr()))
+    return (bins, idx_out) if want_idx else bins
+
+
+def density_query(scene, points, want_color=True, want_mask=False):
+    """points (B,3,N) -> density (B,1,N), color (B,3,N) | None, part mask (B,N) int32 | None."""
+    B, _, N = points.shape
+    dev = points.device
+    den = torch.empty(B, 1, N, device=dev)
+    col = torch.empty(B, 3, N, device=dev) if want_color else None
+    msk = torch.empty(B, N, device=dev, dtype=torch.int32) if want_mask else None
+    check(lib().enarf_density_query(scene.ref, ptr(points), N, ptr(den), ptr(col, allow_none=True),
+                                    ptr(msk, torch.int32, True), stream_ptr()))
+    return den, col, msk
+
+
+def _render_fine_fwd(scene, dmin, dmax, direction, bins):
+    B, n, Nf = bins.shape
+    dev = bins.device
+    color = torch.empty(B, 3, n, device=dev)
+    mask = torch.empty(B, n, device=dev)
+    disp = torch.empty(B, n, device=dev)
+    fw = torch.empty(B, n, Nf - 1, device=dev)
+    fd = torch.empty(B, n, Nf, device=dev)
+    check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
+                                      ptr(mask), ptr(disp), ptr(fw), ptr(fd), stream_ptr()))
+    return color, mask, disp, fw, fd
+
+
+class RenderFine(torch.autograd.Function):
+    """Fused fine pass.  Differentiable inputs: tri_plane (NCHW, features and probabilities), the three
+    W_eff and the three biases; everything else (pose, rays, bins) carries no gradient, as in the
+    reference (rendering.py:216-217)."""
+
+    @staticmethod
+    def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins)
+        ctx.scene = scene
+        ctx.save_for_backward(dmin, dmax, direction, bins)
+        ctx.tp_shape = tri_plane.shape
+        ctx.mark_non_differentiable(out[4])
+        return out
+
+    @staticmethod
+    def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd):
+        scene = ctx.scene
+        dmin, dmax, direction, bins = ctx.saved_tensors
+        B, n, Nf = bins.shape
+        dev = bins.device
+        c = lambda g: None if g is None else g.contiguous().float()
+        need_tp = ctx.needs_input_grad[5]
+        d_tp = torch.zeros(ctx.tp_shape, device=dev)
+        d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
+        d_prob = d_tp[:, FEAT_DIM * 3:]
+        dw = [torch.zeros_like(w) for w in scene.w]
+        db = [torch.zeros_like(b) for b in scene.b]
+        g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
+        check(lib().enarf_render_fine_bwd(
+            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf,
+            ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
+            ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
+            ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+        if need_tp:
+            unpack_plane_grads(d_feat, d_tp)
+        return (None, None, None, None, None, d_tp if need_tp else None, dw[0], dw[1], dw[2],
+                db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
+
+
+def ctx_shape(scene, i):
+    return scene.b_shapes[i] if hasattr(scene, "b_shapes") else scene.b[i].shape
+
+
+def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None):
+    """-> color (B,3,n), mask (B,n), disparity (B,n), fine_weights (B,n,Nf-1), fine_depth (B,n,Nf).
+    Pass the autograd-tracked ``tri_plane`` and ``decoder`` tensors to get gradients."""
+    if tri_plane is None or not torch.is_grad_enabled():
+        return _render_fine_fwd(scene, dmin, dmax, direction, bins)
+    (w1, b1), (w2, b2), (w3, b3) = decoder
+    scene.b_shapes = [b1.shape, b2.shape, b3.shape]
+    return RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)

@@ -1,0 +1,137 @@
+/* enarf_b200.h -- C ABI of libenarf_b200.so: the B200 (sm_100a) articulated tri-plane renderer hot path.
+ *
+ * Drop-in boundary for nogu-atsu/ENARF-GAN (reference paths below are relative to that repo):
+ *   - replaces the pybind module `triplane_sampler_cuda` (cuda_extension/TriplaneSampler.cpp:15-59);
+ *   - supplies fused kernels for what libraries/NeRF/rendering.py:10-359, libraries/triplane/sampling.py:9-127,
+ *     models/narf.py:147-275 and libraries/triplane/triplane_nerf.py:32-48 do with ~60 eager torch ops.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its comment says "host"; the caller owns every buffer
+ *     (outputs, zero-initialised gradient buffers, scratch); the library never allocates or retains them;
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); calls are asynchronous and
+ *     never synchronise the device; the current device must be the one owning the pointers;
+ *   - every function returns 0 on success or an ENARF_ERR_* code; enarf_last_error() gives the message of
+ *     the last failure on the calling thread; no exceptions cross the boundary;
+ *   - all floating-point buffers are fp32 unless stated; tensors are dense row-major with the shape given.
+ */
+#ifndef ENARF_B200_H
+#define ENARF_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ENARF_OK 0
+#define ENARF_ERR_INVALID_ARG 1   /* null pointer, bad size, unsupported mode */
+#define ENARF_ERR_UNSUPPORTED 2   /* shape outside what the kernels are built for */
+#define ENARF_ERR_CUDA 3          /* launch / runtime failure (message has the CUDA error string) */
+
+#define ENARF_FEAT_DIM 32         /* tri-plane feature channels per plane (models/narf.py:21) */
+#define ENARF_HIDDEN 64           /* decoder width (models/narf.py:75: StyledMLP(32, 64, 4)) */
+#define ENARF_MAX_PARTS 32        /* part mask is one uint32 */
+
+#define ENARF_DTYPE_F32 0
+#define ENARF_DTYPE_BF16 1
+
+#define ENARF_RNG_GIVEN 0         /* bin indices + jitter supplied by the caller (torch.multinomial parity) */
+#define ENARF_RNG_PHILOX 1        /* in-kernel Philox4x32-10 inverse-CDF sampling */
+
+/* Everything constant across one render call (one generator forward). */
+typedef struct enarf_scene {
+    int32_t B;                    /* samples in the batch */
+    int32_t P;                    /* parts after transform_pose (23 or 24), <= ENARF_MAX_PARTS */
+    int32_t H, W;                 /* tri-plane resolution (256 x 256 in the reference) */
+    const float* pose;            /* (B,P,4,4) part->camera frames, translation already x coordinate_scale
+                                     (libraries/NARF/pose_utils.py:129-148, rendering.py:258-260) */
+    const float* cscale;          /* (B,P) canonical_bone_length / bone_length / coordinate_scale (narf.py:165) */
+    const float* canon_pose;      /* (P,4,4) canonical part frames (narf.py:84-120) */
+    const void* feat_planes;      /* (B,3,H,W,32) channels-last feature planes made by enarf_repack_planes */
+    int32_t feat_dtype;           /* ENARF_DTYPE_F32 | ENARF_DTYPE_BF16 */
+    int32_t reserved0;
+    const float* prob_planes;     /* NCHW part-probability planes: element [b][3*p+k][y][x] at
+                                     prob_planes + b*prob_batch_stride + ((3*p+k)*H + y)*W + x (narf.py:239) */
+    int64_t prob_batch_stride;    /* elements between consecutive samples of prob_planes */
+    const float* w1;              /* (B,64,32) per-sample modulated, normalised decoder weights */
+    const float* w2;              /* (B,64,64)   (libraries/custom_stylegan2/net.py:229-247) */
+    const float* w3;              /* (B,4,64) */
+    const float* b1;              /* (64)  StyledConv.bias (net.py:299) */
+    const float* b2;              /* (64) */
+    const float* b3;              /* (4) */
+} enarf_scene_t;
+
+/* Message of the last error raised on this thread ("" if none). */
+const char* enarf_last_error(void);
+/* Library / ABI version, e.g. 100 = 0.1.0. */
+int enarf_version(void);
+
+/* NCHW tri-plane (B, C_total, H, W) fp32 -> channels-last feature planes (B,3,H,W,32) in out_dtype.
+ * Channel 32*k+c of the input becomes [b][k][y][x][c] (channel order of sampling.py:28). */
+int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_total, int H, int W,
+                        void* feat_out, int out_dtype, void* stream);
+/* Gradient of the above: d_feat (B,3,H,W,32) fp32 is ADDED into d_tri_plane_nchw channels [0,96). */
+int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W,
+                             float* d_tri_plane_nchw, void* stream);
+
+/* Batch-global near/far (rendering.py:15-17): nearfar[0] = max(min tz - sqrt3, near0),
+ * nearfar[1] = max(max tz + sqrt3, far0) over all B*P part translations of `pose`. */
+int enarf_near_far(const float* pose, int B, int P, float near0, float far0, float* nearfar, void* stream);
+
+/* decide_frustrum_range (rendering.py:10-79).  image_coord (B,3,n) homogeneous pixels; inv_K (B,3,3);
+ * outputs depth_min/depth_max (B,n), ray_dir (B,3,n), validity (B,n) uint8 (1 = some probe in some part). */
+int enarf_depth_range(const float* image_coord, const float* inv_K, const float* pose, const float* nearfar,
+                      int B, int P, int n, float* depth_min, float* depth_max, float* ray_dir,
+                      uint8_t* validity, void* stream);
+
+/* Coarse pass (rendering.py:119-190 + narf.py:176-275, no gradient): Nc stratified mid-points per ray ->
+ * density -> alpha weights -> max-blur + 0.01.  weights_out (B,n,Nc); density_out (B,n,Nc) optional (NULL). */
+int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
+                        const float* ray_dir, int n, int Nc, float* weights_out, float* density_out,
+                        void* stream);
+
+/* Hierarchical sampling (rendering.py:192-197): per ray draw Nf bins from the blurred coarse weights,
+ * bins = idx/Nc + jitter/Nc, sorted ascending.  weights (R,Nc).  mode GIVEN: idx (R,Nf) int32 and jitter
+ * (R,Nf) are inputs.  mode PHILOX: counter = (ray_id_offset + ray, sample), key = seed; idx_out optional. */
+int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, const int32_t* idx,
+                      const float* jitter, uint64_t seed, int64_t ray_id_offset, float* bins_out,
+                      int32_t* idx_out, void* stream);
+
+/* Fine pass forward, fused gather -> decoder -> compositing (rendering.py:198-200,283-335).
+ * bins (B,n,Nf) sorted.  Outputs: color (B,3,n), mask (B,n), disparity (B,n),
+ * fine_weights (B,n,Nf-1), fine_depth (B,n,Nf). */
+int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
+                          const float* ray_dir, const float* bins, int n, int Nf, float* color, float* mask,
+                          float* disparity, float* fine_weights, float* fine_depth, void* stream);
+
+/* Fine pass backward.  Upstream gradients (any may be NULL = zero): g_color (B,3,n), g_mask (B,n),
+ * g_disparity (B,n), g_fine_weights (B,n,Nf-1).  Gradient buffers (caller zero-initialises; results are
+ * ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as scene->prob_planes,
+ * d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4). */
+int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
+                          const float* ray_dir, const float* bins, int n, int Nf, const float* g_color,
+                          const float* g_mask, const float* g_disparity, const float* g_fine_weights,
+                          float* d_feat, float* d_prob, int64_t d_prob_batch_stride, float* d_w1, float* d_w2,
+                          float* d_w3, float* d_b1, float* d_b2, float* d_b3, void* stream);
+
+/* Point query = calc_density_and_color_from_camera_coord_v2 (models/narf.py:176-211): points (B,3,N) in
+ * the scaled camera frame -> density (B,1,N), color (B,3,N) (NULL to skip), part_mask (B,N) uint32 bit p =
+ * part p valid (NULL to skip). */
+int enarf_density_query(const enarf_scene_t* scene, const float* points, int N, float* density, float* color,
+                        uint32_t* part_mask, void* stream);
+
+/* The literal replacement of triplane_sampler_cuda.triplane_sampler_forward / _backward
+ * (cuda_extension/TriplaneSampler.cpp:15-52, TriplaneSampler_kernel.cu:13-229): input (N,3C,H,W) NCHW,
+ * grid (N,Ho,Wo,3) -> output (N,C,Ho,Wo) = sum over the three planes of the sample at
+ * (x=grid[k], y=grid[(k+1)%3]).  interpolation 0 bilinear | 1 nearest; padding 0 zeros | 1 border | 2 reflection. */
+int enarf_triplane_sample_fwd(const float* input, const float* grid, int N, int C, int H, int W, int Ho, int Wo,
+                              int interpolation, int padding, int align_corners, float* output, void* stream);
+/* grad_input (N,3C,H,W) and grad_grid (N,Ho,Wo,3) are ADDED into (caller zero-initialises); either may be NULL. */
+int enarf_triplane_sample_bwd(const float* grad_output, const float* input, const float* grid, int N, int C,
+                              int H, int W, int Ho, int Wo, int interpolation, int padding, int align_corners,
+                              float* grad_input, float* grad_grid, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ENARF_B200_H */
