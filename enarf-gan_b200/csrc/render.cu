@@ -16,6 +16,7 @@
 #include <cuda_bf16.h>
 
 #include "common.cuh"
+#include "gather.cuh"
 
 #define TP_MAX 512        // points per tile
 #define NT 128            // threads per CTA
@@ -43,6 +44,7 @@ struct RenderArgs {
     float* disp;
     float* fine_weights;
     float* fine_depth;
+    float* point_out;
     float* q_density;
     float* q_color;
     uint32_t* q_mask;
@@ -63,64 +65,6 @@ struct Smem {
     uint16_t list[TP_MAX];
     int n_active;
 };
-
-__device__ __forceinline__ float lrelu_s2(float x) { return (x > 0.f ? x : 0.2f * x) * 1.4142135623730951f; }
-
-// linspace(0,1,Nc+1)[j] under the oracle's contract
-__device__ __forceinline__ float unit_bin(int j, int Nc, float step) {
-    return (j < (Nc + 1) / 2) ? cmul(step, (float)j) : csub(1.0f, cmul(step, (float)(Nc - j)));
-}
-
-template <typename T>
-__device__ __forceinline__ float4 load_feat4(const T* base, long long elem);
-template <>
-__device__ __forceinline__ float4 load_feat4<float>(const float* base, long long elem) {
-    return __ldg(reinterpret_cast<const float4*>(base + elem));
-}
-template <>
-__device__ __forceinline__ float4 load_feat4<__nv_bfloat16>(const __nv_bfloat16* base, long long elem) {
-    uint2 r = __ldg(reinterpret_cast<const uint2*>(base + elem));
-    float4 v;
-    v.x = __uint_as_float(r.x << 16);
-    v.y = __uint_as_float(r.x & 0xffff0000u);
-    v.z = __uint_as_float(r.y << 16);
-    v.w = __uint_as_float(r.y & 0xffff0000u);
-    return v;
-}
-
-// Gather for one point by an 8-lane group: lane l owns feature channels 4l..4l+3.
-template <typename T>
-__device__ __forceinline__ float4 gather_point(const enarf_scene_t& sc, const float* s_part, int b, uint32_t m, float x,
-                                               float y, float z, int lane8) {
-    float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int H = sc.H, W = sc.W;
-    const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * H * W * FEAT;
-    const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
-    while (m) {
-        const int p = __ffs(m) - 1;
-        m &= m - 1;
-        float c[3];
-        part_canonical(s_part + p * PART_STRIDE, x, y, z, c[0], c[1], c[2]);
-        Bilin bl[3];
-        float wp = 1.f;
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
-            wp *= sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const long long base = ((long long)k * H * W + (long long)bl[k].y0 * W + bl[k].x0) * FEAT + lane8 * 4;
-            const float w00 = bl[k].w00 * wp, w01 = bl[k].w01 * wp, w10 = bl[k].w10 * wp, w11 = bl[k].w11 * wp;
-            float4 v;
-            if (w00 != 0.f) { v = load_feat4<T>(feat, base); f.x = fmaf(w00, v.x, f.x); f.y = fmaf(w00, v.y, f.y); f.z = fmaf(w00, v.z, f.z); f.w = fmaf(w00, v.w, f.w); }
-            if (w01 != 0.f) { v = load_feat4<T>(feat, base + FEAT); f.x = fmaf(w01, v.x, f.x); f.y = fmaf(w01, v.y, f.y); f.z = fmaf(w01, v.z, f.z); f.w = fmaf(w01, v.w, f.w); }
-            if (w10 != 0.f) { v = load_feat4<T>(feat, base + (long long)W * FEAT); f.x = fmaf(w10, v.x, f.x); f.y = fmaf(w10, v.y, f.y); f.z = fmaf(w10, v.z, f.z); f.w = fmaf(w10, v.w, f.w); }
-            if (w11 != 0.f) { v = load_feat4<T>(feat, base + (long long)(W + 1) * FEAT); f.x = fmaf(w11, v.x, f.x); f.y = fmaf(w11, v.y, f.y); f.z = fmaf(w11, v.z, f.z); f.w = fmaf(w11, v.w, f.w); }
-        }
-    }
-    return f;
-}
 
 // Decoder for one active point: column `col` of s.act holds the 32 input features on entry.
 // Outer-product form: loop over inputs, 64 statically indexed accumulators, weights broadcast from smem.
@@ -322,6 +266,10 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             }
             continue;
         }
+        if (MODE == MODE_FINE && a.point_out) {
+            float4* dst = reinterpret_cast<float4*>(a.point_out) + ((size_t)b * n + ray0) * S;
+            for (int t = tid; t < tp; t += NT) dst[t] = *reinterpret_cast<const float4*>(s.out + t * 4);
+        }
         const int M = (MODE == MODE_COARSE) ? S : S - 1;  // intervals that carry weight
         for (int r = warp; r < rays; r += NT / 32) {
             const float* dep = s.depth + r * (S + 1);
@@ -437,7 +385,7 @@ extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* dept
 extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                      const float* ray_dir, const float* bins, int n, int Nf, float* color,
                                      float* mask, float* disparity, float* fine_weights, float* fine_depth,
-                                     void* stream) {
+                                     float* point_out, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_fwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && color && mask && disparity && fine_weights && fine_depth,
@@ -459,6 +407,7 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
     a.disp = disparity;
     a.fine_weights = fine_weights;
     a.fine_depth = fine_depth;
+    a.point_out = point_out;
     return launch_render<MODE_FINE>(a, "enarf_render_fine_fwd", (cudaStream_t)stream);
 }
 

@@ -133,7 +133,7 @@ def density_query(scene, points, want_color=True, want_mask=False):
     return den, col, msk
 
 
-def _render_fine_fwd(scene, dmin, dmax, direction, bins):
+def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False):
     B, n, Nf = bins.shape
     dev = bins.device
     color = torch.empty(B, 3, n, device=dev)
@@ -141,9 +141,10 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins):
     disp = torch.empty(B, n, device=dev)
     fw = torch.empty(B, n, Nf - 1, device=dev)
     fd = torch.empty(B, n, Nf, device=dev)
+    pts = torch.empty(B, n, Nf, 4, device=dev) if want_points else None
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
-                                      ptr(mask), ptr(disp), ptr(fw), ptr(fd), stream_ptr()))
-    return color, mask, disp, fw, fd
+                                      ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True), stream_ptr()))
+    return (color, mask, disp, fw, fd, pts) if want_points else (color, mask, disp, fw, fd)
 
 
 class RenderFine(torch.autograd.Function):
@@ -153,17 +154,17 @@ class RenderFine(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins)
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True)
         ctx.scene = scene
-        ctx.save_for_backward(dmin, dmax, direction, bins)
+        ctx.save_for_backward(dmin, dmax, direction, bins, out[5])
         ctx.tp_shape = tri_plane.shape
-        ctx.mark_non_differentiable(out[4])
+        ctx.mark_non_differentiable(out[4], out[5])
         return out
 
     @staticmethod
-    def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd):
+    def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
         scene = ctx.scene
-        dmin, dmax, direction, bins = ctx.saved_tensors
+        dmin, dmax, direction, bins, pts = ctx.saved_tensors
         B, n, Nf = bins.shape
         dev = bins.device
         c = lambda g: None if g is None else g.contiguous().float()
@@ -175,7 +176,7 @@ class RenderFine(torch.autograd.Function):
         db = [torch.zeros_like(b) for b in scene.b]
         g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
         check(lib().enarf_render_fine_bwd(
-            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf,
+            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), n, Nf,
             ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
             ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
             ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
@@ -196,4 +197,4 @@ def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None
         return _render_fine_fwd(scene, dmin, dmax, direction, bins)
     (w1, b1), (w2, b2), (w3, b3) = decoder
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
-    return RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)
+    return RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)[:5]
