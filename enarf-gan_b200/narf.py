@@ -1,0 +1,187 @@
+"""Host-side mirror of the reference's radiance-field model for the tri-plane path.
+
+``TriPlaneNARF`` keeps the reference's constructor, method names, parameter/buffer names (so a reference
+checkpoint's ``nerf.*`` keys load unchanged) and the ``buffers_tensors`` / ``temporal_state`` side effects
+(models/narf.py:17-290, libraries/NARF/base.py:11-83, libraries/NeRF/base.py:11-151); every heavy operation
+is delegated to the fused kernels through ``rendering`` / ``ops``.  The decoder layers mirror
+``StyledMLP`` -> ``StyledConv(conv_1d=True)`` -> ``ModulatedConv1d`` + ``EqualLinear``
+(libraries/NeRF/net.py:10-27, libraries/custom_stylegan2/net.py:128-179,194-254,270-320) but only hold the
+parameters and compute the per-sample effective weights; the convolution itself runs inside the kernels.
+"""
+import math
+from typing import Dict, Optional
+
+import numpy as np
+import torch
+from torch import nn
+
+from . import hostmath, ops, rendering
+
+_UNSUPPORTED = ("selector_mlp", "no_selector", "clamp_mask", "multiply_density_with_triplane_wieght",
+                "constant_trimask", "deformation_field")
+
+
+class EqualLinear(nn.Module):
+    """Parameters of the reference's EqualLinear (weight ~ N(0,1)/lr_mul, runtime scale 1/sqrt(in))."""
+
+    def __init__(self, in_dim, out_dim, bias_init=0.0):
+        super().__init__()
+        self.weight = nn.Parameter(torch.randn(out_dim, in_dim))
+        self.bias = nn.Parameter(torch.full((out_dim,), float(bias_init)))
+        self.scale = 1.0 / math.sqrt(in_dim)
+
+    def forward(self, x):
+        return torch.nn.functional.linear(x, self.weight * self.scale, self.bias)
+
+
+class ModulatedConv1d(nn.Module):
+    """Holds ``weight (1,out,in,1)`` and ``modulation``; ``effective_weight(style)`` is what the reference
+    feeds to its grouped conv1d: normalize_in(weight * style / sqrt(in))."""
+
+    def __init__(self, in_channel, out_channel, style_dim):
+        super().__init__()
+        self.in_channel, self.out_channel = in_channel, out_channel
+        self.scale = 1.0 / math.sqrt(in_channel)
+        self.weight = nn.Parameter(torch.randn(1, out_channel, in_channel, 1))
+        self.modulation = EqualLinear(style_dim, in_channel, bias_init=1.0)
+
+    def effective_weight(self, style):
+        s = self.modulation(style)                                     # (B,in)
+        w = self.scale * self.weight[0, :, :, 0][None] * s[:, None, :]  # (B,out,in)
+        return torch.nn.functional.normalize(w, dim=-1)
+
+
+class _Noise(nn.Module):  # present in the reference's StyledConv even when unused; kept for key parity
+    def __init__(self):
+        super().__init__()
+        self.weight = nn.Parameter(torch.zeros(1))
+
+
+class StyledConv1d(nn.Module):
+    def __init__(self, in_channel, out_channel, style_dim):
+        super().__init__()
+        self.conv = ModulatedConv1d(in_channel, out_channel, style_dim)
+        self.bias = nn.Parameter(torch.zeros(1, out_channel, 1))
+        self.noise = _Noise()
+
+
+class StyledMLP(nn.Module):
+    def __init__(self, in_dim, hidden_dim, out_dim, style_dim=512, num_layers=3):
+        super().__init__()
+        dims = [in_dim] + [hidden_dim] * (num_layers - 1) + [out_dim]
+        self.layers = nn.ModuleList([StyledConv1d(dims[i], dims[i + 1], style_dim) for i in range(num_layers)])
+        self.hidden_dim = hidden_dim
+
+    def effective(self, style):
+        """[(W_eff (B,out,in), bias (out,)), ...] -- autograd-tracked."""
+        return [(l.conv.effective_weight(style), l.bias.reshape(-1)) for l in self.layers]
+
+
+def _cfg(config, key, default=None):
+    if isinstance(config, dict):
+        return config.get(key, default)
+    return getattr(config, key, default)
+
+
+class TriPlaneNARF(nn.Module):
+    tri_plane_based = True
+
+    def __init__(self, config, z_dim=256, num_bone=1, bone_length=True, parent=None, num_bone_param=None,
+                 view_dependent: bool = False, tri_plane_gen: Optional[nn.Module] = None,
+                 plane_dtype=torch.float32):
+        super().__init__()
+        assert bone_length and parent is not None
+        if view_dependent:
+            raise NotImplementedError("view-dependent colour is outside the fused path (SURVEY section 8a, a10)")
+        for key in _UNSUPPORTED:
+            if _cfg(config, key, False):
+                raise NotImplementedError(f"nerf_params.{key} is not supported by the fused renderer")
+        self.config = config
+        self.origin_location = _cfg(config, "origin_location")
+        self.coordinate_scale = _cfg(config, "coordinate_scale", 1)
+        if self.origin_location not in ("center", "center_fixed", "center+head"):
+            raise ValueError(f"origin_location {self.origin_location!r}")       # NeRF/base.py:23
+        self.z_dim, self.z2_dim = (z_dim if isinstance(z_dim, (list, tuple)) else (z_dim, z_dim))
+        self.w_dim, self.feat_dim = 512, 32
+        self.view_dependent = False
+        self.num_bone = num_bone - 1 if self.origin_location in ("center", "center_fixed") else num_bone
+        self.parent_id = np.asarray(parent)
+        self.plane_dtype = plane_dtype
+        self.rng_mode = "torch"      # "torch": the reference's multinomial/uniform_ stream; "philox": in-kernel
+        self.rng_seed = 0
+        self.temporal_state = {}
+        self.buffers_tensors = {}
+        if _cfg(config, "constant_triplane", False):
+            self.tri_plane = nn.Parameter(torch.zeros(1, 32 * 3 + self.num_bone * 3, 256, 256))
+        elif tri_plane_gen is not None:
+            self.tri_plane_gen = tri_plane_gen     # e.g. the StyleGAN2-ADA generator (out of scope here)
+        self.mlp = StyledMLP(32, 64, 4, style_dim=self.z2_dim)
+
+    # ---- canonical pose (models/narf.py:84-120) -------------------------------------------------------
+    def register_canonical_pose(self, pose: np.ndarray) -> None:
+        pose = np.asarray(pose)
+        par = self.parent_id[1:]
+        self.register_buffer("canonical_joints", torch.tensor(pose[1:, :3, 3], dtype=torch.float32))
+        self.register_buffer("canonical_parent_joints", torch.tensor(pose[par, :3, 3], dtype=torch.float32))
+        frames, length = hostmath.canonical_part_frames(pose, self.parent_id, self.origin_location)
+        self.register_buffer("canonical_bone_length", length)
+        self.register_buffer("canonical_pose", frames)
+
+    def transform_pose(self, pose_to_camera, bone_length):
+        return hostmath.part_frames(pose_to_camera, bone_length, self.origin_location, self.parent_id)
+
+    # ---- tri-plane ------------------------------------------------------------------------------------
+    def compute_tri_plane_feature(self, z, bone_length, truncation_psi=1):
+        if hasattr(self, "tri_plane"):
+            return self.tri_plane.expand(z.shape[0], -1, -1, -1)
+        if not hasattr(self, "tri_plane_gen"):
+            raise RuntimeError("no tri-plane source: pass constant_triplane=True, a tri_plane_gen module or "
+                               "model_input['tri_plane_feature']")
+        return self.tri_plane_gen(z, bone_length, truncation_psi=truncation_psi)
+
+    def build_scene(self, pose_scaled, model_input: Dict):
+        """SceneBuffers for one render call + the autograd-tracked tensors behind it."""
+        bone_length, z, z_rend = model_input["bone_length"], model_input["z"], model_input["z_rend"]
+        tri_plane = model_input.get("tri_plane_feature")
+        if tri_plane is None:
+            tri_plane = self.compute_tri_plane_feature(z, bone_length, model_input.get("truncation_psi", 1))
+        tri_plane = tri_plane.to(torch.float32).contiguous()      # materialises an expanded constant plane
+        self.buffers_tensors["tri_plane_feature"] = tri_plane      # narf.py:194
+        if not self.training:
+            self.temporal_state["tri_plane_feature"] = tri_plane
+        decoder = self.mlp.effective(z_rend)
+        cscale = (self.canonical_bone_length[None, :, None] / bone_length / self.coordinate_scale)[:, :, 0]
+        scene = ops.SceneBuffers(pose_scaled, cscale, self.canonical_pose, tri_plane, decoder, self.plane_dtype)
+        return scene, tri_plane, decoder
+
+    # ---- point query (models/narf.py:176-211) ---------------------------------------------------------
+    def calc_density_and_color_from_camera_coord_v2(self, position, pose_to_camera, ray_direction, model_input):
+        """position (B,3,n) in the scaled camera frame -> density (B,1,n), color (B,3,n).  Forward only."""
+        scene, _, _ = self.build_scene(pose_to_camera, model_input)
+        with torch.no_grad():
+            den, col, _ = ops.density_query(scene, position.to(torch.float32).contiguous())
+        return den, col
+
+    # ---- NARFBase.forward / render_entire_img (libraries/NARF/base.py:26-63) --------------------------
+    def forward(self, batchsize, sampled_img_coord, pose_to_camera, inv_intrinsics, z, z_rend, bone_length,
+                render_scale=1, Nc=64, Nf=128, return_intermediate=False, truncation_psi=1,
+                camera_pose: Optional[torch.Tensor] = None, return_disparity=False):
+        model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
+        pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
+        out = rendering.render(self, sampled_img_coord, pose_to_camera, inv_intrinsics, render_scale=render_scale,
+                               Nc=Nc, Nf=Nf, return_intermediate=return_intermediate, camera_pose=camera_pose,
+                               model_input=model_input)
+        if return_intermediate:
+            color, mask, _, inter = out
+            return color, mask, inter
+        color, mask, disparity = out
+        return (color, mask, disparity) if return_disparity else (color, mask)
+
+    def render_entire_img(self, pose_to_camera, inv_intrinsics, z, z_rend, bone_length, camera_pose=None,
+                          render_size=128, Nc=64, Nf=128, semantic_map=False, use_normalized_intrinsics=False,
+                          no_grad=True, truncation_psi=1, bbox=None):
+        model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
+        pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
+        model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
+        return rendering.render_entire_img(self, pose_to_camera, inv_intrinsics, camera_pose, render_size, Nc, Nf,
+                                           semantic_map, use_normalized_intrinsics, no_grad, model_input, bbox=bbox)

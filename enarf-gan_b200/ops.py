@@ -190,11 +190,14 @@ def ctx_shape(scene, i):
     return scene.b_shapes[i] if hasattr(scene, "b_shapes") else scene.b[i].shape
 
 
-def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None):
-    """-> color (B,3,n), mask (B,n), disparity (B,n), fine_weights (B,n,Nf-1), fine_depth (B,n,Nf).
+def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None, want_points=None):
+    """-> color (B,3,n), mask (B,n), disparity (B,n), fine_weights (B,n,Nf-1), fine_depth (B,n,Nf)
+    [, points (B,n,Nf,4) = per-sample (r,g,b,sigma) when ``want_points`` is given (None/False/True)].
     Pass the autograd-tracked ``tri_plane`` and ``decoder`` tensors to get gradients."""
     if tri_plane is None or not torch.is_grad_enabled():
-        return _render_fine_fwd(scene, dmin, dmax, direction, bins)
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=bool(want_points))
+        return out if want_points is None or want_points else out + (None,)
     (w1, b1), (w2, b2), (w3, b3) = decoder
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
-    return RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)[:5]
+    out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)
+    return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))

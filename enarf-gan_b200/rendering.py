@@ -26,7 +26,7 @@ def pixel_grid(render_size, patch_size, batchsize, device):
 
 def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rng="philox", seed=0,
                 idx=None, jitter=None, compact_b1=True, tri_plane=None, decoder=None, nearfar=None,
-                generator=None, return_intermediate=False):
+                generator=None, return_intermediate=False, want_points=False):
     """image_coord (B,3,n) homogeneous pixels -> dict(color (B,3,n), mask (B,n), disparity (B,n),
     fine_weights (B,n',Nf-1), fine_depth (B,n',Nf), validity (B,n)); n' = valid rays when B == 1
     (rendering.py:107-110), else n.
@@ -65,13 +65,113 @@ def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rn
             bins = ops.fine_sample(wb, Nf, idx=idx.reshape(B, n, Nf), jitter=jitter.reshape(B, n, Nf))
         else:
             raise ValueError(f"unknown rng mode {rng!r}")
-    color, mask, disp, fw, fd = ops.render_fine(scene, dmin, dmax, direction, bins, tri_plane, decoder)
+    color, mask, disp, fw, fd, pts = ops.render_fine(scene, dmin, dmax, direction, bins, tri_plane, decoder,
+                                                     want_points=want_points)
     if sel is not None:                             # rendering.py:337-350
         full_c = torch.zeros(B, 3, n_all, device=dev).index_copy(2, sel, color)
         full_m = torch.zeros(B, n_all, device=dev).index_copy(1, sel, mask)
         full_d = torch.zeros(B, n_all, device=dev).index_copy(1, sel, disp)
         color, mask, disp = full_c, full_m, full_d
-    out.update(color=color, mask=mask, disparity=disp, fine_weights=fw, fine_depth=fd)
+    out.update(color=color, mask=mask, disparity=disp, fine_weights=fw, fine_depth=fd, points=pts)
     if return_intermediate:
         out.update(coarse_weights_blurred=wb, bins=bins, depth_min=dmin, depth_max=dmax, direction=direction)
     return out
+
+
+# ------------------------------------------------------------------------------------------------------
+# Drop-in signatures of the reference module (libraries/NeRF/rendering.py:227-427)
+# ------------------------------------------------------------------------------------------------------
+def _scaled(model, pose_to_camera):
+    if model.coordinate_scale != 1:                      # rendering.py:258-260
+        pose_to_camera = pose_to_camera.clone()
+        pose_to_camera[:, :, :3, 3] *= model.coordinate_scale
+    return pose_to_camera
+
+
+def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: float = 1, Nc: int = 64,
+           Nf: int = 128, semantic_map: bool = False, return_intermediate: bool = False,
+           camera_pose: Optional[torch.Tensor] = None, model_input: Dict = {}, _scene=None):
+    """Same contract as the reference's ``render``: image_coord (B,1,3,n), pose_to_camera (B,P,4,4) part
+    frames -> (color (B,3,n), mask (B,n), disparity (B,n)[, (fine_points, fine_density)]); stores
+    ``model.buffers_tensors["fine_weights"|"fine_depth"|"fine_density"]`` ((B,1,n',Nf-1), (B,1,n',Nf),
+    (B,1,n'*Nf)) like rendering.py:287,323-324."""
+    if render_scale != 1:
+        raise NotImplementedError("render_scale != 1 is never used by the reference's callers")
+    if semantic_map:
+        raise NotImplementedError("semantic map rendering is disabled in the reference too (rendering.py:299)")
+    if pose_to_camera.requires_grad:
+        raise NotImplementedError("Currently pose should not be differentiable")     # rendering.py:216-217
+    B, _, _, n_all = image_coord.shape
+    pose_scaled = _scaled(model, pose_to_camera)
+    if not hasattr(model, "buffers_tensors"):
+        model.buffers_tensors = {}
+    if _scene is None:
+        _scene = model.build_scene(pose_scaled, model_input)
+    scene, tri_plane, decoder = _scene
+    track = torch.is_grad_enabled() and (tri_plane.requires_grad or any(w.requires_grad for w, _ in decoder))
+    out = render_rays(scene, image_coord.reshape(B, 3, n_all), inv_intrinsics, Nc, Nf,
+                      rng=getattr(model, "rng_mode", "torch"), seed=getattr(model, "rng_seed", 0),
+                      idx=getattr(model, "rng_given", (None, None))[0],
+                      jitter=getattr(model, "rng_given", (None, None))[1],
+                      tri_plane=tri_plane if track else None, decoder=decoder if track else None,
+                      return_intermediate=return_intermediate or not model.training, want_points=True)
+    if getattr(model, "rng_mode", "torch") == "philox":
+        model.rng_seed = getattr(model, "rng_seed", 0) + 1      # fresh draws on the next call
+    if out["fine_weights"] is not None:
+        n = out["fine_weights"].shape[1]
+        model.buffers_tensors["fine_weights"] = out["fine_weights"][:, None]
+        model.buffers_tensors["fine_depth"] = out["fine_depth"][:, None]
+        model.buffers_tensors["fine_density"] = out["points"][..., 3].reshape(B, 1, n * Nf)
+        if not model.training:
+            model.temporal_state.update(fine_depth=out["fine_depth"][:, None],
+                                        fine_density=out["points"][..., :-1, 3][:, None],
+                                        coarse_weights=out["coarse_weights_blurred"].reshape(B * n, Nc))
+    if return_intermediate:
+        inter = None
+        if out["fine_weights"] is not None:
+            u = out["bins"][:, None]                                                      # (B,1,n,Nf)
+            start = (out["depth_min"][:, None] * out["direction"])[..., None]
+            end = (out["depth_max"][:, None] * out["direction"])[..., None]
+            fine_points = (start * (1 - u) + end * u).reshape(B, 3, -1)
+            inter = (fine_points, model.buffers_tensors["fine_density"])
+        return out["color"], out["mask"], out["disparity"], inter
+    return out["color"], out["mask"], out["disparity"]
+
+
+def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Optional[torch.Tensor] = None,
+                      render_size: int = 128, Nc: int = 64, Nf: int = 128, semantic_map: bool = False,
+                      use_normalized_intrinsics: bool = False, no_grad: bool = True, model_input: Dict = {},
+                      bbox=None):
+    """Chunked full-image render with the reference's ``render_bs`` semantics (rendering.py:362-427): batch
+    forced to 1, pixel centres (optionally bbox-cropped / normalised), chunks of ``model.config.render_bs``
+    rays rendered independently and concatenated.  The scene (repacked planes, decoder weights) is built once."""
+    cfg = model.config
+    ray_batchsize = cfg["render_bs"] if isinstance(cfg, dict) else cfg.render_bs
+    if bbox is not None:
+        width, height = bbox[2] - bbox[0], bbox[3] - bbox[1]
+        x_off, y_off = bbox[0], bbox[1]
+    else:
+        width, height, x_off, y_off = render_size, render_size, 0, 0
+    dev = pose_to_camera.device
+    ar = torch.arange(width * height, device=dev)
+    x = (ar % width + 0.5 + x_off).float()
+    y = (torch.div(ar, width, rounding_mode="floor") + 0.5 + y_off).float()
+    if use_normalized_intrinsics:
+        x, y = x / render_size, y / render_size
+    img_coord = torch.stack([x, y, torch.ones_like(x)], dim=0)[None, None]                # (1,1,3,n)
+    pose1 = pose_to_camera[:1]
+    mi = dict(model_input)
+    for key in ("z", "z_rend", "bone_length", "tri_plane_feature"):
+        if mi.get(key) is not None:
+            mi[key] = mi[key][:1]
+    colors, masks, disps = [], [], []
+    with torch.set_grad_enabled(not no_grad):
+        scene = model.build_scene(_scaled(model, pose1), mi)
+        for i in range(0, img_coord.shape[-1], ray_batchsize):
+            c, m, d = render(model, img_coord[:, :, :, i:i + ray_batchsize], pose1, inv_intrinsics, Nc=Nc, Nf=Nf,
+                             camera_pose=camera_pose, model_input=mi, _scene=scene)
+            colors.append(c)
+            masks.append(m)
+            disps.append(d)
+        color, mask, disp = torch.cat(colors, dim=2), torch.cat(masks, dim=1), torch.cat(disps, dim=1)
+    return color.reshape(3, height, width), mask.reshape(height, width), disp.reshape(height, width)

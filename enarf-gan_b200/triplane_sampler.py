@@ -1,0 +1,54 @@
+"""Drop-in for ``cuda_extension/triplane_sampler.py`` (reference lines 7-68): same enum maps, same
+``TriplaneSamplerFunction`` / ``triplane_sampler`` signatures, backed by ``enarf_triplane_sample_fwd/bwd``.
+
+Deliberate differences from the reference, both documented in DESIGN.md:
+  * backward returns the gradients the caller asked for (the reference's wrapper returns ``None`` exactly when
+    a gradient is required, ``triplane_sampler.py:59-62``, so it never trains anything);
+  * ``mode='nearest'`` sums the three planes like ``'bilinear'`` does (the reference's nearest branch overwrites
+    the output per plane, ``TriplaneSampler_kernel.cu:79-88``, so only the last plane survives).
+"""
+import torch
+
+from ._abi import check, lib, ptr, stream_ptr
+
+GRID_SAMPLE_INTERPOLATION_MODES = {"bilinear": 0, "nearest": 1}
+GRID_SAMPLE_PADDING_MODES = {"zeros": 0, "border": 1, "reflection": 2}
+
+
+class TriplaneSamplerFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, input, grid, mode="bilinear", padding_mode="zeros", align_corners=False,
+                output_mask=(True, True)):
+        """input (N,3C,H,W), grid (N,h,w,3) -> (N,C,h,w): sum over the three planes of the sample at
+        (x=grid[...,k], y=grid[...,(k+1)%3])."""
+        mode_enum = GRID_SAMPLE_INTERPOLATION_MODES[mode]
+        padding_enum = GRID_SAMPLE_PADDING_MODES[padding_mode]
+        inp = input.detach().float().contiguous()
+        grd = grid.detach().float().contiguous()
+        N, C3, H, W = inp.shape
+        assert C3 % 3 == 0 and grd.shape[0] == N and grd.shape[-1] == 3
+        C, Ho, Wo = C3 // 3, grd.shape[1], grd.shape[2]
+        out = torch.empty(N, C, Ho, Wo, device=inp.device)
+        check(lib().enarf_triplane_sample_fwd(ptr(inp), ptr(grd), N, C, H, W, Ho, Wo, mode_enum, padding_enum,
+                                              int(bool(align_corners)), ptr(out), stream_ptr()))
+        ctx.save_for_backward(inp, grd)
+        ctx.cfg = (mode_enum, padding_enum, int(bool(align_corners)), tuple(output_mask))
+        return out.to(input.dtype)
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        inp, grd = ctx.saved_tensors
+        mode_enum, padding_enum, align, output_mask = ctx.cfg
+        N, C3, H, W = inp.shape
+        C, Ho, Wo = C3 // 3, grd.shape[1], grd.shape[2]
+        g_in = torch.zeros_like(inp) if output_mask[0] else None
+        g_grid = torch.zeros_like(grd) if output_mask[1] else None
+        check(lib().enarf_triplane_sample_bwd(ptr(grad_output.float().contiguous()), ptr(inp), ptr(grd), N, C, H, W,
+                                              Ho, Wo, mode_enum, padding_enum, align, ptr(g_in, allow_none=True),
+                                              ptr(g_grid, allow_none=True), stream_ptr()))
+        return g_in, g_grid, None, None, None, None
+
+
+def triplane_sampler(input, grid, mode="bilinear", padding_mode="zeros", align_corners=False):
+    output_mask = (input.requires_grad, grid.requires_grad)
+    return TriplaneSamplerFunction.apply(input, grid, mode, padding_mode, align_corners, output_mask)
