@@ -43,3 +43,26 @@ int enarf_check_scene(const enarf_scene_t* sc, const char* who) {
                   "%s: NULL decoder buffers", who);
     return ENARF_OK;
 }
+
+// Dynamic tile scheduling needs one zeroed int per launch.  The library must not allocate, so the counters are
+// slots of a static device array handed out round-robin: launches stay independent unless more than
+// ENARF_COUNTER_SLOTS of them are in flight at once.
+#define ENARF_COUNTER_SLOTS 4096
+__device__ int g_tile_counters[ENARF_COUNTER_SLOTS];
+static unsigned g_next_slot = 0;
+
+int* enarf_tile_counter(cudaStream_t stream) {
+    int* base = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&base, g_tile_counters);
+    if (e != cudaSuccess) {
+        enarf_set_error("enarf_tile_counter: %s", cudaGetErrorString(e));
+        return nullptr;
+    }
+    const unsigned slot = __atomic_fetch_add(&g_next_slot, 1u, __ATOMIC_RELAXED) % ENARF_COUNTER_SLOTS;
+    e = cudaMemsetAsync(base + slot, 0, sizeof(int), stream);
+    if (e != cudaSuccess) {
+        enarf_set_error("enarf_tile_counter: %s", cudaGetErrorString(e));
+        return nullptr;
+    }
+    return base + slot;
+}

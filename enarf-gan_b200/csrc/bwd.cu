@@ -39,6 +39,7 @@ struct BwdArgs {
     long long d_prob_stride;
     float *d_w1, *d_w2, *d_w3, *d_b1, *d_b2, *d_b3;
     int n, S, rays_per_tile, tiles_per_sample;
+    int* tile_counter;
 };
 
 struct BSmem {
@@ -258,7 +259,13 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
     WGrad wg;
     wgrad_zero(wg);
 
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    __shared__ int s_tile;
+    for (;;) {
+        __syncthreads();  // everyone is done with the previous tile (and with s_tile)
+        if (tid == 0) s_tile = atomicAdd(a.tile_counter, 1);
+        __syncthreads();
+        const int tile = s_tile;
+        if (tile >= total_tiles) break;
         const int b = tile / a.tiles_per_sample;
         const int ray0 = (tile - b * a.tiles_per_sample) * a.rays_per_tile;
         const int rays = min(a.rays_per_tile, n - ray0);
@@ -544,6 +551,8 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     const int total = scene->B * a.tiles_per_sample;
     const int grid = min(total, enarf_sm_count());
     const size_t smem = sizeof(BSmem);
+    a.tile_counter = enarf_tile_counter((cudaStream_t)stream);
+    if (!a.tile_counter) return ENARF_ERR_CUDA;
     cudaError_t e;
     if (scene->feat_dtype == ENARF_DTYPE_F32) {
         auto k = render_bwd_kernel<float>;

@@ -32,6 +32,9 @@ void enarf_set_error(const char* fmt, ...);
 
 int enarf_check_scene(const enarf_scene_t* sc, const char* who);
 int enarf_sm_count();
+// Per-launch dynamic-tile-scheduler counter: a slot of a static device array, zeroed on `stream` before use.
+// Returns nullptr on failure (error string set).
+int* enarf_tile_counter(cudaStream_t stream);
 
 // ---- contract arithmetic: every product / sum rounded separately, never contracted ------------
 // (oracle/enarf_oracle.py "ARITHMETIC CONTRACT"; these feed the bit-exact masks and indices)
@@ -139,3 +142,45 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
     return c;
 }
 __device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }
+
+// Same predicate as part_canonical() with an early exit after the in-cube test (identical arithmetic, so the
+// resulting bit is identical); used where the canonical coordinates themselves are not needed.
+__device__ __forceinline__ bool part_valid(const float* q, float x, float y, float z) {
+    float l0, l1, l2;
+    if (!part_local(q, x, y, z, l0, l1, l2)) return false;
+    float s0 = cmul(l0, q[12]), s1 = cmul(l1, q[12]), s2 = cmul(l2, q[12]);
+    float c0 = cadd(cdot3(q[13], q[14], q[15], s0, s1, s2), q[22]);
+    float c1 = cadd(cdot3(q[16], q[17], q[18], s0, s1, s2), q[23]);
+    float c2 = cadd(cdot3(q[19], q[20], q[21], s0, s1, s2), q[24]);
+    return fabsf(c0) < 1.f && fabsf(c1) < 1.f && fabsf(c2) < 1.f;
+}
+
+// Conservative ray/part pre-filter.  The segment start + u*(end-start), u in [0,1], is clipped against the
+// part cube inflated to |local| <= 1 + CULL_MARGIN; a point whose u lies outside [u0,u1] cannot pass the
+// exact in-cube test (the margin is ~1000x the worst fp32 rounding of the contract arithmetic at these
+// magnitudes), so skipping the exact test there cannot change a mask bit.  Returns false if empty.
+#define CULL_MARGIN 2e-3f
+__device__ __forceinline__ bool ray_part_interval(const float* q, float sx, float sy, float sz, float ex, float ey,
+                                                  float ez, float& u0, float& u1) {
+    const float ax = sx - q[9], ay = sy - q[10], az = sz - q[11];
+    const float bx = ex - sx, by = ey - sy, bz = ez - sz;
+    u0 = -1e-3f;
+    u1 = 1.f + 1e-3f;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const float A = q[i] * ax + q[3 + i] * ay + q[6 + i] * az;   // local coordinate at u = 0
+        const float Bd = q[i] * bx + q[3 + i] * by + q[6 + i] * bz;  // d(local)/du
+        const float lim = 1.f + CULL_MARGIN + 1e-5f * (fabsf(A) + fabsf(Bd));
+        if (fabsf(Bd) < 1e-12f) {
+            if (fabsf(A) > lim) return false;
+        } else {
+            const float inv = 1.f / Bd;
+            float t0 = (-lim - A) * inv, t1 = (lim - A) * inv;
+            if (t0 > t1) { const float t = t0; t0 = t1; t1 = t; }
+            const float pad = 1e-5f * (fabsf(t0) + fabsf(t1)) + 1e-6f;
+            u0 = fmaxf(u0, t0 - pad);
+            u1 = fminf(u1, t1 + pad);
+        }
+    }
+    return u0 <= u1;
+}

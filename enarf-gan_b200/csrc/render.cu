@@ -3,25 +3,30 @@
 // Reference being replaced: libraries/NeRF/rendering.py:119-335, models/narf.py:147-275,
 // libraries/triplane/sampling.py:54-127, libraries/triplane/triplane_nerf.py:32-48.
 //
-// One CTA owns whole rays (a tile of rays x samples <= TP_MAX points) so that per-point features,
-// activations, densities and colours live only in shared memory / registers:
-//   phase 1  every point: position (contract arithmetic), 24 slab tests -> uint32 part mask; the points that
-//            hit at least one part are compacted into a list (the rest have density 0 by narf.py:204);
-//   phase 2  per chunk of 128 active points: 8 lanes per point gather the channels-last feature texels with
+// One CTA (256 threads, 2 CTAs/SM) owns whole rays (a tile of rays x samples <= TP_MAX points) so that
+// per-point features, activations, densities and colours live only in shared memory / registers:
+//   phase 0  per (ray, part): conservative slab clip of the ray segment against the part cube -> candidate
+//            part mask + parameter interval per ray (exactness argument: common.cuh ray_part_interval);
+//   phase 1  every point: position (contract arithmetic), exact slab tests for the candidate parts only ->
+//            uint32 part mask; points that hit at least one part are compacted into a list (the others have
+//            density 0 by narf.py:204 and never reach the decoder);
+//   phase 2  per chunk of 256 active points: 8 lanes per point gather the channels-last feature texels with
 //            128-bit loads (12 full 128-B lines per valid part), weighted by prod sigmoid(prob planes);
-//            then one thread per point runs the 32->64->64->4 decoder against weights staged in smem;
+//            then one thread per point runs the 32->64->64->4 decoder: layer 1 as an outer product over the
+//            inputs (64 register accumulators, transposed weights broadcast from smem), layers 2+3 as row dot
+//            products folded straight into the 4 outputs, so no activation ever goes back to shared memory;
 //   phase 3  one warp per ray: shuffle scan of sigma*delta -> transmittance -> weights -> colour/mask/disparity.
-// The grid is persistent (a multiple of the SM count) and strides over tiles in sample-major order so one
-// sample's planes stay L2-resident and decoder weights are reloaded only when the sample changes.
+// The grid is persistent (2 x SM count) and strides over tiles in sample-major order so one sample's planes
+// stay L2-resident and decoder weights are reloaded only when the sample changes.
 #include <cuda_bf16.h>
 
 #include "common.cuh"
 #include "gather.cuh"
 
-#define TP_MAX 512        // points per tile
-#define NT 128            // threads per CTA
-#define CHUNK 128         // active points decoded per pass
-#define ACT_STRIDE 129    // smem activation column stride (conflict-free for both gather writes and MLP reads)
+#define TP_MAX 1024       // points per tile
+#define NT 256            // threads per CTA
+#define CHUNK 256         // active points decoded per pass
+#define FS 257            // feature column stride (conflict-free for the gather writes and the decoder reads)
 #define MAX_RAYS 16       // rays per tile upper bound
 
 enum { MODE_COARSE = 0, MODE_FINE = 1, MODE_QUERY = 2 };
@@ -37,6 +42,7 @@ struct RenderArgs {
     int S;              // samples per ray (1 in query mode)
     int rays_per_tile;  // rays (query: points) per tile
     int tiles_per_sample;
+    int* tile_counter;
     float* weights_out;
     float* density_out;
     float* color;
@@ -51,30 +57,31 @@ struct RenderArgs {
 };
 
 struct Smem {
-    float w1t[FEAT * HID];   // [i][o] transposed decoder weights
-    float w2t[HID * HID];
-    float w3[4 * HID];       // [c][o]
+    float w1t[FEAT * HID];   // [i][o]  layer 1, transposed
+    float w2[HID * HID];     // [o][i]  layer 2, as stored
+    float w3t[HID * 4];      // [o][c]  layer 3, transposed
     float b1[HID], b2[HID], b3[4];
     float part[ENARF_MAX_PARTS * PART_STRIDE];
-    float act[HID * ACT_STRIDE];
+    float feat[FEAT * FS];
     float pos[TP_MAX * 3];
     float out[TP_MAX * 4];   // r,g,b,sigma per point
     float depth[TP_MAX + MAX_RAYS];
     float ray[MAX_RAYS * 5];  // dmin,dmax,dx,dy,dz
+    float cull[MAX_RAYS * ENARF_MAX_PARTS * 2];  // u0,u1 per (ray, part)
+    uint32_t cand[MAX_RAYS];                     // candidate part mask per ray
     uint32_t pmask[TP_MAX];
     uint16_t list[TP_MAX];
     int n_active;
 };
 
-// Decoder for one active point: column `col` of s.act holds the 32 input features on entry.
-// Outer-product form: loop over inputs, 64 statically indexed accumulators, weights broadcast from smem.
-__device__ __forceinline__ void decode_point(Smem& s, int col, float& r, float& g, float& bl, float& sigma_raw) {
+// Decoder for one active point whose 32 features sit in column `col` of s.feat.
+__device__ __forceinline__ float4 decode_point(const Smem& s, int col) {
     float h[HID];
 #pragma unroll
     for (int o = 0; o < HID; ++o) h[o] = s.b1[o];
 #pragma unroll 2
     for (int i = 0; i < FEAT; ++i) {
-        const float xi = s.act[i * ACT_STRIDE + col];
+        const float xi = s.feat[i * FS + col];
         const float4* w = reinterpret_cast<const float4*>(s.w1t + i * HID);
 #pragma unroll
         for (int o4 = 0; o4 < HID / 4; ++o4) {
@@ -86,48 +93,47 @@ __device__ __forceinline__ void decode_point(Smem& s, int col, float& r, float& 
         }
     }
 #pragma unroll
-    for (int o = 0; o < HID; ++o) s.act[o * ACT_STRIDE + col] = lrelu_s2(h[o]);
-#pragma unroll
-    for (int o = 0; o < HID; ++o) h[o] = s.b2[o];
-#pragma unroll 2
-    for (int i = 0; i < HID; ++i) {
-        const float xi = s.act[i * ACT_STRIDE + col];
-        const float4* w = reinterpret_cast<const float4*>(s.w2t + i * HID);
-#pragma unroll
-        for (int o4 = 0; o4 < HID / 4; ++o4) {
-            const float4 v = w[o4];
-            h[4 * o4 + 0] = fmaf(v.x, xi, h[4 * o4 + 0]);
-            h[4 * o4 + 1] = fmaf(v.y, xi, h[4 * o4 + 1]);
-            h[4 * o4 + 2] = fmaf(v.z, xi, h[4 * o4 + 2]);
-            h[4 * o4 + 3] = fmaf(v.w, xi, h[4 * o4 + 3]);
-        }
-    }
+    for (int o = 0; o < HID; ++o) h[o] = lrelu_s2(h[o]);
     float o3[4] = {s.b3[0], s.b3[1], s.b3[2], s.b3[3]};
-#pragma unroll
+#pragma unroll 2
     for (int o = 0; o < HID; ++o) {
-        const float a = lrelu_s2(h[o]);
+        const float4* w = reinterpret_cast<const float4*>(s.w2 + o * HID);
+        float a0 = s.b2[o], a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) o3[c] = fmaf(s.w3[c * HID + o], a, o3[c]);
+        for (int i4 = 0; i4 < HID / 4; ++i4) {
+            const float4 v = w[i4];
+            a0 = fmaf(v.x, h[4 * i4 + 0], a0);
+            a1 = fmaf(v.y, h[4 * i4 + 1], a1);
+            a2 = fmaf(v.z, h[4 * i4 + 2], a2);
+            a3 = fmaf(v.w, h[4 * i4 + 3], a3);
+        }
+        const float act = lrelu_s2((a0 + a1) + (a2 + a3));
+        const float4 w3 = *reinterpret_cast<const float4*>(s.w3t + o * 4);
+        o3[0] = fmaf(w3.x, act, o3[0]);
+        o3[1] = fmaf(w3.y, act, o3[1]);
+        o3[2] = fmaf(w3.z, act, o3[2]);
+        o3[3] = fmaf(w3.w, act, o3[3]);
     }
-    r = tanhf(lrelu_s2(o3[0]));
-    g = tanhf(lrelu_s2(o3[1]));
-    bl = tanhf(lrelu_s2(o3[2]));
-    sigma_raw = lrelu_s2(o3[3]);
+    // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl. the last is
+    // conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318)
+    return make_float4(tanhf(lrelu_s2(o3[0])), tanhf(lrelu_s2(o3[1])), tanhf(lrelu_s2(o3[2])),
+                       fmaxf(lrelu_s2(o3[3]), 0.f) * 10.f);
 }
 
 __device__ __forceinline__ void load_decoder(Smem& s, const enarf_scene_t& sc, int b, int tid) {
     const float* w1 = sc.w1 + (size_t)b * HID * FEAT;
     const float* w2 = sc.w2 + (size_t)b * HID * HID;
     const float* w3 = sc.w3 + (size_t)b * 4 * HID;
-    for (int e = tid; e < HID * FEAT; e += NT) {  // coalesced read of [o][i], transposed store [i][o]
-        int o = e / FEAT, i = e - o * FEAT;
-        s.w1t[i * HID + o] = w1[e];
+    for (int e = tid; e < HID * FEAT; e += NT) {   // e = i*HID + o: conflict-free smem store, strided L2 read
+        const int i = e / HID, o = e - i * HID;
+        s.w1t[e] = w1[o * FEAT + i];
     }
-    for (int e = tid; e < HID * HID; e += NT) {
-        int o = e / HID, i = e - o * HID;
-        s.w2t[i * HID + o] = w2[e];
+    for (int e = tid; e < HID * HID / 4; e += NT)
+        reinterpret_cast<float4*>(s.w2)[e] = reinterpret_cast<const float4*>(w2)[e];
+    for (int e = tid; e < 4 * HID; e += NT) {
+        const int o = e >> 2, c = e & 3;
+        s.w3t[e] = w3[c * HID + o];
     }
-    for (int e = tid; e < 4 * HID; e += NT) s.w3[e] = w3[e];
     if (tid < HID) {
         s.b1[tid] = sc.b1[tid];
         s.b2[tid] = sc.b2[tid];
@@ -141,11 +147,18 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
     Smem& s = *reinterpret_cast<Smem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const enarf_scene_t& sc = a.sc;
-    const int S = a.S, n = a.n;
+    const int S = a.S, n = a.n, P = sc.P;
     const int total_tiles = sc.B * a.tiles_per_sample;
+    const float cstep = (MODE == MODE_COARSE) ? __fdiv_rn(1.0f, (float)S) : 0.f;
     int cur_b = -1;
 
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    __shared__ int s_tile;
+    for (;;) {
+        __syncthreads();  // everyone is done with the previous tile (and with s_tile)
+        if (tid == 0) s_tile = atomicAdd(a.tile_counter, 1);
+        __syncthreads();
+        const int tile = s_tile;
+        if (tile >= total_tiles) break;
         const int b = tile / a.tiles_per_sample;
         const int ray0 = (tile - b * a.tiles_per_sample) * a.rays_per_tile;
         const int rays = min(a.rays_per_tile, n - ray0);
@@ -165,10 +178,27 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             s.ray[tid * 5 + 2] = d[0];
             s.ray[tid * 5 + 3] = d[n];
             s.ray[tid * 5 + 4] = d[2 * (size_t)n];
+            s.cand[tid] = 0;
         }
         __syncthreads();
 
-        // ---- phase 1: positions, part masks, compaction ------------------------------------------
+        // ---- phase 0: conservative ray/part clip ----------------------------------------------------
+        if (MODE != MODE_QUERY) {
+            for (int e = tid; e < rays * P; e += NT) {
+                const int r = e / P, p = e - r * P;
+                const float* ry = s.ray + r * 5;
+                float u0, u1;
+                if (ray_part_interval(s.part + p * PART_STRIDE, ry[0] * ry[2], ry[0] * ry[3], ry[0] * ry[4],
+                                      ry[1] * ry[2], ry[1] * ry[3], ry[1] * ry[4], u0, u1)) {
+                    s.cull[(r * ENARF_MAX_PARTS + p) * 2] = u0;
+                    s.cull[(r * ENARF_MAX_PARTS + p) * 2 + 1] = u1;
+                    atomicOr(&s.cand[r], 1u << p);
+                }
+            }
+            __syncthreads();
+        }
+
+        // ---- phase 1: positions, exact part masks, compaction -----------------------------------------
         for (int t = tid; t < ((tp + 31) & ~31); t += NT) {
             uint32_t m = 0;
             if (t < tp) {
@@ -178,24 +208,27 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                     x = pt[0];
                     y = pt[n];
                     z = pt[2 * (size_t)n];
+                    for (int p = 0; p < P; ++p)
+                        if (part_valid(s.part + p * PART_STRIDE, x, y, z)) m |= 1u << p;
                 } else {
                     const int r = t / S, j = t - r * S;
                     const float* ry = s.ray + r * 5;
                     const float dmin = ry[0], dmax = ry[1];
                     const float sx = cmul(dmin, ry[2]), sy = cmul(dmin, ry[3]), sz = cmul(dmin, ry[4]);
                     const float ex = cmul(dmax, ry[2]), ey = cmul(dmax, ry[3]), ez = cmul(dmax, ry[4]);
+                    float u;
                     if (MODE == MODE_COARSE) {
                         // mid-point of consecutive stratified edges (rendering.py:125-131)
-                        const float step = __fdiv_rn(1.0f, (float)S);
-                        const float t0 = unit_bin(j, S, step), t1 = unit_bin(j + 1, S, step);
+                        const float t0 = unit_bin(j, S, cstep), t1 = unit_bin(j + 1, S, cstep);
                         x = cmul(cadd(clerp(sx, ex, t1), clerp(sx, ex, t0)), 0.5f);
                         y = cmul(cadd(clerp(sy, ey, t1), clerp(sy, ey, t0)), 0.5f);
                         z = cmul(cadd(clerp(sz, ez, t1), clerp(sz, ez, t0)), 0.5f);
                         s.depth[r * (S + 1) + j] = clerp(dmin, dmax, t0);
                         if (j == S - 1) s.depth[r * (S + 1) + S] = clerp(dmin, dmax, t1);
+                        u = 0.5f * (t0 + t1);
                     } else {
                         const size_t o = ((size_t)b * n + ray0 + r) * S + j;
-                        const float u = a.bins[o];
+                        u = a.bins[o];
                         x = clerp(sx, ex, u);
                         y = clerp(sy, ey, u);
                         z = clerp(sz, ez, u);
@@ -203,10 +236,14 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                         s.depth[r * (S + 1) + j] = dep;
                         a.fine_depth[o] = dep;
                     }
-                }
-                for (int p = 0; p < sc.P; ++p) {
-                    float c0, c1, c2;
-                    if (part_canonical(s.part + p * PART_STRIDE, x, y, z, c0, c1, c2)) m |= 1u << p;
+                    uint32_t cm = s.cand[r];
+                    const float* cu = s.cull + r * ENARF_MAX_PARTS * 2;
+                    while (cm) {
+                        const int p = __ffs(cm) - 1;
+                        cm &= cm - 1;
+                        if (u >= cu[2 * p] && u <= cu[2 * p + 1] && part_valid(s.part + p * PART_STRIDE, x, y, z))
+                            m |= 1u << p;
+                    }
                 }
                 s.pos[t * 3 + 0] = x;
                 s.pos[t * 3 + 1] = y;
@@ -225,7 +262,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
         __syncthreads();
         const int n_active = s.n_active;
 
-        // ---- phase 2: gather + decode, CHUNK active points at a time -----------------------------
+        // ---- phase 2: gather + decode, CHUNK active points at a time ---------------------------------
         for (int c0 = 0; c0 < n_active; c0 += CHUNK) {
             const int cnt = min(CHUNK, n_active - c0);
             const int lane8 = tid & 7;
@@ -233,24 +270,18 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 const int t = s.list[c0 + q];
                 const float4 f = gather_point<T>(sc, s.part, b, s.pmask[t], s.pos[t * 3], s.pos[t * 3 + 1],
                                                  s.pos[t * 3 + 2], lane8);
-                float* dst = s.act + (lane8 * 4) * ACT_STRIDE + q;
+                float* dst = s.feat + (lane8 * 4) * FS + q;
                 dst[0] = f.x;
-                dst[ACT_STRIDE] = f.y;
-                dst[2 * ACT_STRIDE] = f.z;
-                dst[3 * ACT_STRIDE] = f.w;
+                dst[FS] = f.y;
+                dst[2 * FS] = f.z;
+                dst[3 * FS] = f.w;
             }
             __syncthreads();
-            if (tid < cnt) {
-                const int t = s.list[c0 + tid];
-                float r, g, bl, sr;
-                decode_point(s, tid, r, g, bl, sr);
-                // density = relu(raw) * 10 (narf.py:274); the any-valid gate (narf.py:204) is implicit
-                *reinterpret_cast<float4*>(s.out + t * 4) = make_float4(r, g, bl, fmaxf(sr, 0.f) * 10.f);
-            }
+            if (tid < cnt) *reinterpret_cast<float4*>(s.out + s.list[c0 + tid] * 4) = decode_point(s, tid);
             __syncthreads();
         }
 
-        // ---- phase 3: outputs ----------------------------------------------------------------------
+        // ---- phase 3: outputs ---------------------------------------------------------------------------
         if (MODE == MODE_QUERY) {
             for (int t = tid; t < tp; t += NT) {
                 const float4 o = *reinterpret_cast<const float4*>(s.out + t * 4);
@@ -339,6 +370,8 @@ static int launch_render(RenderArgs& a, const char* who, cudaStream_t stream) {
     const int total = a.sc.B * a.tiles_per_sample;
     const int grid = min(total, 2 * enarf_sm_count());
     const size_t smem = sizeof(Smem);
+    a.tile_counter = enarf_tile_counter(stream);
+    if (!a.tile_counter) return ENARF_ERR_CUDA;
     cudaError_t e;
     if (a.sc.feat_dtype == ENARF_DTYPE_F32) {
         auto k = render_kernel<MODE, float>;
@@ -392,6 +425,8 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
                   ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: NULL argument");
     ENARF_REQUIRE(n > 0 && Nf >= 2, ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: bad sizes n=%d Nf=%d", n, Nf);
     ENARF_REQUIRE(Nf <= TP_MAX, ENARF_ERR_UNSUPPORTED, "enarf_render_fine_fwd: Nf=%d exceeds %d", Nf, TP_MAX);
+    ENARF_REQUIRE(!point_out || ((uintptr_t)point_out & 15) == 0, ENARF_ERR_INVALID_ARG,
+                  "enarf_render_fine_fwd: point_out must be 16-byte aligned");
     RenderArgs a = {};
     a.sc = *scene;
     a.dmin = depth_min;
