@@ -1,0 +1,389 @@
+// Tile framework shared by the fused forward (render.cu) and backward (bwd.cu) kernels.
+//
+// One CTA of 512 threads (16 warps, one CTA per SM, persistent with a dynamic tile counter) owns whole rays:
+// a tile is rays x samples <= TP_MAX points.  Per tile
+//   phase 0  per (ray, part): conservative clip of the ray segment against the part cube (common.cuh);
+//   phase 1  per point: position (contract arithmetic), exact part tests on the candidates -> part mask;
+//            points inside at least one part are compacted into `list`; a prefix sum of popc(mask) over
+//            the list gives every active point its range of (point, part) pairs;
+//   chunks   <= CH active points and <= PB pairs at a time:
+//     setup    ONE thread per (point, part) pair: canonical coordinates, three bilinear footprints, the
+//              twelve probability texels, sigmoid product -> a 20-word record in shared memory
+//              (the old kernels redid this on each of the 8 lanes that gather a point);
+//     gather   8 lanes per point walk the point's records: 12 x 128-bit texel loads per pair, lane l owns
+//              channels 4l..4l+3; features land in X[channel][point];
+//     decoder  register-tiled FP32 GEMMs over the chunk (4 points x 4 outputs per thread), activations
+//              stay in shared memory as [channel][point] rows of stride AS.
+// Why FP32 FFMA and not tensor cores: the parity bar is 1e-4 on fp32 outputs; measured on B200
+// (profiles/mma_rate_r1.txt) mma.sync tf32 issues 139 TMAC/s and bf16 278 TMAC/s against 36 TMAC/s of FFMA, so an
+// error-compensated 3xTF32 / 6xBF16 split lands at ~46 TMAC/s -- no better than FFMA once the split and
+// fragment shuffles are paid.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "gather.cuh"
+
+#define NT 512             // threads per CTA
+#define NWARP (NT / 32)
+#define CH 128             // active points per chunk
+#define AS 132             // activation row stride in floats (rows 16-B aligned, row r starts at bank 4r)
+#define W1S 36             // decoder weight row strides: consecutive rows start 4 banks apart
+#define W2S 68
+#define TP_MAX 1024        // points per tile
+#define MAX_RAYS 32        // rays per tile
+#define PB 512             // (point, part) pair records per chunk
+#define REC 20             // words per record; 20*r mod 32 hits 8 distinct 4-bank groups for r..r+7
+static_assert(TP_MAX == 2 * NT, "the prefix scan handles two list entries per thread");
+
+// record layout (words): 0..2 element offset of texel (y0,x0) of plane k inside the sample's feature planes,
+// 3 part id, 4..15 bilinear weights [k][corner] (forward: already multiplied by the part weight),
+// 16 part weight wp = prod sigmoid, 17..19 sigmoid(prob sample k)
+struct __align__(16) DecoderSmem {
+    float w1[HID * W1S];   // [o][i]
+    float w2[HID * W2S];   // [o][i]
+    float w3[4 * W2S];     // [c][o]
+    float b1[HID], b2[HID], b3[4];
+    float pad_[12];
+};
+
+struct __align__(16) TileSmem {
+    float4 pm[TP_MAX];                 // x, y, z, part mask (bits)
+    float depth[TP_MAX + MAX_RAYS];
+    float ray[MAX_RAYS * 8];           // dmin, dmax, dx, dy, dz
+    uint32_t cand[MAX_RAYS];
+    uint16_t list[TP_MAX];
+    uint16_t pref[TP_MAX + 8];
+    int wsum[NWARP];
+    int n_active;
+    int tile;
+    int pad_[2];
+};
+
+union __align__(16) RecSmem {
+    float rec[PB * REC];
+    float cull[MAX_RAYS * ENARF_MAX_PARTS * 2];   // phase 0/1 only
+};
+
+__device__ __forceinline__ void load_decoder_smem(DecoderSmem& d, const enarf_scene_t& sc, int b, int tid) {
+    const float* w1 = sc.w1 + (size_t)b * HID * FEAT;
+    const float* w2 = sc.w2 + (size_t)b * HID * HID;
+    const float* w3 = sc.w3 + (size_t)b * 4 * HID;
+    for (int e = tid; e < HID * FEAT; e += NT) d.w1[(e / FEAT) * W1S + (e % FEAT)] = w1[e];
+    for (int e = tid; e < HID * HID; e += NT) d.w2[(e / HID) * W2S + (e % HID)] = w2[e];
+    for (int e = tid; e < 4 * HID; e += NT) d.w3[(e / HID) * W2S + (e % HID)] = w3[e];
+    if (tid < HID) {
+        d.b1[tid] = sc.b1[tid];
+        d.b2[tid] = sc.b2[tid];
+    }
+    if (tid < 4) d.b3[tid] = sc.b3[tid];
+}
+
+// ---- phase 0 + 1 --------------------------------------------------------------------------------------
+enum { TILE_COARSE = 0, TILE_FINE = 1, TILE_QUERY = 2 };
+
+struct TileGeom {
+    const float *dmin, *dmax, *dir, *bins, *points;
+    float* fine_depth;   // optional global copy of the per-sample depth (fine forward only)
+    int n, S;
+    int skip_last;       // backward: the last sample of a ray only closes the last interval, no gradient
+};
+
+// Loads the tile's rays, clips them against the parts and fills pm / depth / list / pref.  Ends synchronised.
+template <int MODE>
+__device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float* s_part, const TileGeom& g, int P,
+                                            int b, int ray0, int rays, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const int S = g.S, n = g.n, tp = rays * S;
+    if (tid == 0) t.n_active = 0;
+    if (MODE != TILE_QUERY && tid < rays) {
+        const size_t o = (size_t)b * n + ray0 + tid;
+        const float* d = g.dir + (size_t)b * 3 * n + ray0 + tid;
+        t.ray[tid * 8 + 0] = g.dmin[o];
+        t.ray[tid * 8 + 1] = g.dmax[o];
+        t.ray[tid * 8 + 2] = d[0];
+        t.ray[tid * 8 + 3] = d[n];
+        t.ray[tid * 8 + 4] = d[2 * (size_t)n];
+        t.cand[tid] = 0;
+    }
+    __syncthreads();
+    if (MODE != TILE_QUERY) {
+        for (int e = tid; e < rays * P; e += NT) {
+            const int rr = e / P, p = e - rr * P;
+            const float* ry = t.ray + rr * 8;
+            float u0, u1;
+            if (ray_part_interval(s_part + p * PART_STRIDE, ry[0] * ry[2], ry[0] * ry[3], ry[0] * ry[4], ry[1] * ry[2],
+                                  ry[1] * ry[3], ry[1] * ry[4], u0, u1)) {
+                r.cull[(rr * ENARF_MAX_PARTS + p) * 2] = u0;
+                r.cull[(rr * ENARF_MAX_PARTS + p) * 2 + 1] = u1;
+                atomicOr(&t.cand[rr], 1u << p);
+            }
+        }
+        __syncthreads();
+    }
+    const float cstep = (MODE == TILE_COARSE) ? __fdiv_rn(1.0f, (float)S) : 0.f;
+    for (int i = tid; i < ((tp + 31) & ~31); i += NT) {
+        uint32_t m = 0;
+        if (i < tp) {
+            float x, y, z;
+            if (MODE == TILE_QUERY) {
+                const float* pt = g.points + (size_t)b * 3 * n + ray0 + i;
+                x = pt[0];
+                y = pt[n];
+                z = pt[2 * (size_t)n];
+                for (int p = 0; p < P; ++p)
+                    if (part_valid(s_part + p * PART_STRIDE, x, y, z)) m |= 1u << p;
+            } else {
+                const int rr = i / S, j = i - rr * S;
+                const float* ry = t.ray + rr * 8;
+                const float dmin = ry[0], dmax = ry[1];
+                const float sx = cmul(dmin, ry[2]), sy = cmul(dmin, ry[3]), sz = cmul(dmin, ry[4]);
+                const float ex = cmul(dmax, ry[2]), ey = cmul(dmax, ry[3]), ez = cmul(dmax, ry[4]);
+                float u;
+                if (MODE == TILE_COARSE) {
+                    // mid-point of consecutive stratified edges (rendering.py:125-131)
+                    const float t0 = unit_bin(j, S, cstep), t1 = unit_bin(j + 1, S, cstep);
+                    x = cmul(cadd(clerp(sx, ex, t1), clerp(sx, ex, t0)), 0.5f);
+                    y = cmul(cadd(clerp(sy, ey, t1), clerp(sy, ey, t0)), 0.5f);
+                    z = cmul(cadd(clerp(sz, ez, t1), clerp(sz, ez, t0)), 0.5f);
+                    t.depth[rr * (S + 1) + j] = clerp(dmin, dmax, t0);
+                    if (j == S - 1) t.depth[rr * (S + 1) + S] = clerp(dmin, dmax, t1);
+                    u = 0.5f * (t0 + t1);
+                } else {
+                    const size_t o = ((size_t)b * n + ray0 + rr) * S + j;
+                    u = g.bins[o];
+                    x = clerp(sx, ex, u);
+                    y = clerp(sy, ey, u);
+                    z = clerp(sz, ez, u);
+                    const float dep = clerp(dmin, dmax, u);
+                    t.depth[rr * (S + 1) + j] = dep;
+                    if (g.fine_depth) g.fine_depth[o] = dep;
+                }
+                if (!(g.skip_last && j == S - 1)) {
+                    uint32_t cm = t.cand[rr];
+                    const float* cu = r.cull + rr * ENARF_MAX_PARTS * 2;
+                    while (cm) {
+                        const int p = __ffs(cm) - 1;
+                        cm &= cm - 1;
+                        if (u >= cu[2 * p] && u <= cu[2 * p + 1] && part_valid(s_part + p * PART_STRIDE, x, y, z))
+                            m |= 1u << p;
+                    }
+                }
+            }
+            t.pm[i] = make_float4(x, y, z, __uint_as_float(m));
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, m != 0);
+        if (bal) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(&t.n_active, __popc(bal));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (m) t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)i;
+        }
+    }
+    __syncthreads();
+    // exclusive prefix of pairs-per-point over the active list (2 entries per thread)
+    const int na = t.n_active;
+    const int i0 = 2 * tid;
+    const int c0 = i0 < na ? __popc(__float_as_uint(t.pm[t.list[i0]].w)) : 0;
+    const int c1 = i0 + 1 < na ? __popc(__float_as_uint(t.pm[t.list[i0 + 1]].w)) : 0;
+    const int s2 = c0 + c1;
+    int incl = s2;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) t.wsum[warp] = incl;
+    __syncthreads();
+    int base = 0;
+    for (int w = 0; w < warp; ++w) base += t.wsum[w];
+    const int excl = base + incl - s2;
+    if (i0 <= na) t.pref[i0] = (uint16_t)excl;
+    if (i0 + 1 <= na) t.pref[i0 + 1] = (uint16_t)(excl + c0);
+    if (i0 + 2 == na && tid == NT - 1) t.pref[na] = (uint16_t)(excl + s2);   // na == 2*NT: nobody owns pref[na]
+    __syncthreads();
+}
+
+// End (exclusive) of the chunk starting at active index a: at most CH points and PB pairs.
+__device__ __forceinline__ int chunk_end(const TileSmem& t, int a) {
+    const int na = t.n_active;
+    int e = min(a + CH, na);
+    const int p0 = t.pref[a];
+    if (t.pref[e] - p0 > PB) {
+        int lo = a + 1, hi = e;   // invariant: pref[lo]-p0 <= PB (one point has <= 32 pairs), answer in [lo, hi)
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (t.pref[mid] - p0 <= PB) lo = mid; else hi = mid;
+        }
+        e = lo;
+    }
+    return e;
+}
+
+// ---- pair setup: one thread per (point, part) pair of the chunk [a, e) --------------------------------
+// PREMUL: store bilinear weights already multiplied by the part weight (forward); otherwise raw (backward).
+template <bool PREMUL>
+__device__ __forceinline__ void setup_pairs(const TileSmem& t, float* rec, const float* s_part, const enarf_scene_t& sc,
+                                            int b, int a, int e, int tid) {
+    const int p0 = t.pref[a], npairs = t.pref[e] - p0;
+    const int H = sc.H, W = sc.W;
+    const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
+    for (int r = tid; r < npairs; r += NT) {
+        const int target = p0 + r;
+        int lo = a, hi = e;   // largest q in [a, e) with pref[q] <= target
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (t.pref[mid] <= target) lo = mid; else hi = mid;
+        }
+        const float4 pm = t.pm[t.list[lo]];
+        uint32_t m = __float_as_uint(pm.w);
+        for (int k = target - t.pref[lo]; k > 0; --k) m &= m - 1;
+        const int p = __ffs(m) - 1;
+        float c[3];
+        part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
+        Bilin bl[3];
+        float sg[3], wp = 1.f;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
+            sg[k] = sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
+            wp *= sg[k];
+        }
+        const float ws = PREMUL ? wp : 1.f;
+        float4* dst = reinterpret_cast<float4*>(rec + r * REC);
+        int off[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) off[k] = (k * H * W + bl[k].y0 * W + bl[k].x0) * FEAT;
+        dst[0] = make_float4(__int_as_float(off[0]), __int_as_float(off[1]), __int_as_float(off[2]), __int_as_float(p));
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            dst[1 + k] = make_float4(bl[k].w00 * ws, bl[k].w01 * ws, bl[k].w10 * ws, bl[k].w11 * ws);
+        dst[4] = make_float4(wp, sg[0], sg[1], sg[2]);
+    }
+}
+
+// ---- gather: 8 lanes per point, lane l owns channels 4l..4l+3; writes X[channel][q] -------------------
+// SCALE: multiply the stored weights by the part weight on the fly (records hold raw weights).
+template <typename T, bool SCALE>
+__device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec, float* X, const enarf_scene_t& sc,
+                                             int b, int a, int e, int tid) {
+    const int lane8 = tid & 7, cnt = e - a, p0 = t.pref[a];
+    const int W = sc.W;
+    const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * sc.H * W * FEAT + lane8 * 4;
+    const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
+    for (int q = tid >> 3; q < cnt; q += NT / 8) {
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int r1 = t.pref[a + q + 1] - p0;
+        for (int r = t.pref[a + q] - p0; r < r1; ++r) {
+            const float4* rp = reinterpret_cast<const float4*>(rec + r * REC);
+            const float4 o4 = rp[0];
+            const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+            const float ws = SCALE ? rp[4].x : 1.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float4 w4 = rp[1 + k];
+                const float w[4] = {w4.x * ws, w4.y * ws, w4.z * ws, w4.w * ws};
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    if (w[c] != 0.f) {
+                        const float4 v = load_feat4<T>(feat, (long long)off[k] + corner[c]);
+                        f.x = fmaf(w[c], v.x, f.x);
+                        f.y = fmaf(w[c], v.y, f.y);
+                        f.z = fmaf(w[c], v.z, f.z);
+                        f.w = fmaf(w[c], v.w, f.w);
+                    }
+                }
+            }
+        }
+        float* dst = X + (lane8 * 4) * AS + q;
+        dst[0] = f.x;
+        dst[AS] = f.y;
+        dst[2 * AS] = f.z;
+        dst[3 * AS] = f.w;
+    }
+    // columns [cnt, roundup32(cnt)) feed the decoder tiles of the last partially filled warp: keep them finite
+    const int cend = (cnt + 31) & ~31;
+    for (int i = tid; i < FEAT * (cend - cnt); i += NT) {
+        const int row = i / (cend - cnt), col = cnt + i - row * (cend - cnt);
+        X[row * AS + col] = 0.f;
+    }
+}
+
+// ---- register-tiled FP32 GEMMs over one chunk ---------------------------------------------------------
+// Thread tile: 4 consecutive points (quad pq) x 4 outputs.  acc[p][j].
+// (1) weights stored [out][k] (k contiguous): out rows og + 16 j, four k per step.
+template <int K, int WS>
+__device__ __forceinline__ void gemm_kvec(const float* __restrict__ act, const float* __restrict__ Wm, int pq, int og,
+                                          float (&acc)[4][4]) {
+#pragma unroll 2
+    for (int k = 0; k < K; k += 4) {
+        float4 w[4], x[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = *reinterpret_cast<const float4*>(Wm + (og + 16 * j) * WS + k);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * pq);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                acc[0][j] = fmaf(x[i].x, wj[i], acc[0][j]);
+                acc[1][j] = fmaf(x[i].y, wj[i], acc[1][j]);
+                acc[2][j] = fmaf(x[i].z, wj[i], acc[2][j]);
+                acc[3][j] = fmaf(x[i].w, wj[i], acc[3][j]);
+            }
+        }
+    }
+}
+
+// (2) weights stored [k][in] (in contiguous): out[pt][i0+i] = sum_k G[k][pt] * Wm[k][i0+i], NI = 4 or 2.
+template <int K, int WS, int NI>
+__device__ __forceinline__ void gemm_kmajor(const float* __restrict__ G, const float* __restrict__ Wm, int pq, int i0,
+                                            float (&acc)[4][NI]) {
+#pragma unroll 4
+    for (int k = 0; k < K; ++k) {
+        const float4 g = *reinterpret_cast<const float4*>(G + k * AS + 4 * pq);
+        float w[NI];
+        if (NI == 4) {
+            const float4 v = *reinterpret_cast<const float4*>(Wm + k * WS + i0);
+            w[0] = v.x; w[1] = v.y; w[NI - 2] = v.z; w[NI - 1] = v.w;
+        } else {
+            const float2 v = *reinterpret_cast<const float2*>(Wm + k * WS + i0);
+            w[0] = v.x; w[1] = v.y;
+        }
+#pragma unroll
+        for (int i = 0; i < NI; ++i) {
+            acc[0][i] = fmaf(g.x, w[i], acc[0][i]);
+            acc[1][i] = fmaf(g.y, w[i], acc[1][i]);
+            acc[2][i] = fmaf(g.z, w[i], acc[2][i]);
+            acc[3][i] = fmaf(g.w, w[i], acc[3][i]);
+        }
+    }
+}
+
+// (3) weight gradient: acc[j][jj] += sum over quads q = h, h+KS, ... < nquads of
+//     G[ot + 16 j][4q..4q+3] . A[it + IS jj][4q..4q+3]
+template <int KS, int IS>
+__device__ __forceinline__ void wgrad_tile(const float* __restrict__ G, const float* __restrict__ A, int ot, int it,
+                                           int h, int nquads, float (&acc)[4][4], float (&bsum)[4]) {
+    for (int q = h; q < nquads; q += KS) {
+        float4 g[4], x[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[j] = *reinterpret_cast<const float4*>(G + (ot + 16 * j) * AS + 4 * q);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) x[j] = *reinterpret_cast<const float4*>(A + (it + IS * j) * AS + 4 * q);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+#pragma unroll
+            for (int jj = 0; jj < 4; ++jj) {
+                float s = acc[j][jj];
+                s = fmaf(g[j].x, x[jj].x, s);
+                s = fmaf(g[j].y, x[jj].y, s);
+                s = fmaf(g[j].z, x[jj].z, s);
+                s = fmaf(g[j].w, x[jj].w, s);
+                acc[j][jj] = s;
+            }
+            if (it == 0) bsum[j] += (g[j].x + g[j].y) + (g[j].z + g[j].w);
+        }
+    }
+}
