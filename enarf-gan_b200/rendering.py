@@ -175,3 +175,33 @@ def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Option
             disps.append(d)
         color, mask, disp = torch.cat(colors, dim=2), torch.cat(masks, dim=1), torch.cat(disps, dim=1)
     return color.reshape(3, height, width), mask.reshape(height, width), disp.reshape(height, width)
+
+
+# ------------------------------------------------------------------------------------------------------
+# Multi-GPU: sample-major ray sharding.  No data-path collective; the only cross-sample
+# quantity of the reference is the batch-global near/far (rendering.py:15-17), exchanged as two floats.
+# ------------------------------------------------------------------------------------------------------
+def shard_samples(batch: int, rank: int, world: int):
+    """Contiguous block of samples rendered by ``rank`` (sizes differ by at most one)."""
+    base, extra = divmod(batch, world)
+    start = rank * base + min(rank, extra)
+    return start, start + base + (1 if rank < extra else 0)
+
+
+def global_near_far(pose_local, near0: float = NEAR_PLANE, far0: float = FAR_PLANE, group=None):
+    """near/far over the WHOLE batch from this rank's shard of the (scaled) part frames (B_local,P,4,4).
+
+    near = max(min t_z - sqrt3, near0), far = max(max t_z + sqrt3, far0) (rendering.py:15-17); the min / max
+    over ranks is one all_reduce each on a single float (NCCL on GPUs, gloo in the CPU tests).  Returns the
+    2-element tensor ``ops.depth_range(..., nearfar=)`` expects; with no process group it is the local value.
+    """
+    import torch.distributed as dist
+    tz = pose_local[:, :, 2, 3].to(torch.float32)
+    lo, hi = tz.min().reshape(1), tz.max().reshape(1)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    sqrt3 = 3 ** 0.5
+    near = torch.clamp_min(lo - sqrt3, near0)
+    far = torch.clamp_min(hi + sqrt3, far0)
+    return torch.cat([near, far])

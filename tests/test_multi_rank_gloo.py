@@ -1,0 +1,59 @@
+"""World-size-2 gloo test of the N>1 host logic (runs on CPU): sample sharding and the batch-global near/far
+exchange that keeps a ray-sharded render identical to the single-process one."""
+import os
+import socket
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, pose, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from enarf_gan_b200 import rendering
+        lo, hi = rendering.shard_samples(pose.shape[0], rank, world)
+        nf = rendering.global_near_far(pose[lo:hi])
+        torch.save({"range": (lo, hi), "nearfar": nf}, os.path.join(out_dir, f"r{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_shard_samples_partitions_the_batch():
+    from enarf_gan_b200 import rendering
+    for B in (1, 2, 7, 8, 32):
+        for world in (1, 2, 3, 8):
+            blocks = [rendering.shard_samples(B, r, world) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == B
+            assert all(a[1] == b[0] for a, b in zip(blocks, blocks[1:]))
+            sizes = [b[1] - b[0] for b in blocks]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_global_near_far_matches_single_process(tmp_path):
+    import enarf_oracle as O
+    from enarf_gan_b200 import synthetic as S
+    inp = S.make_inputs(5, 16, seed=77)
+    pose, _ = O.transform_pose(inp["pose_to_camera"], inp["bone_length"], "center+head", S.SMPL_PARENTS)
+    pose = pose.clone()
+    pose[:, :, :3, 3] *= 3          # coordinate_scale (rendering.py:258-260)
+    near, far = O.near_far(pose)
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), pose, str(tmp_path)), nprocs=world, join=True)
+    got = [torch.load(os.path.join(tmp_path, f"r{r}.pt")) for r in range(world)]
+    assert got[0]["range"] == (0, 3) and got[1]["range"] == (3, 5)
+    for g in got:   # every rank holds the full-batch scalars, bit-identical to the oracle's
+        assert torch.equal(g["nearfar"], torch.stack([near, far]).float())
