@@ -50,7 +50,9 @@ struct __align__(16) BwdSmem {
 __device__ __forceinline__ float act_grad(float a) { return (a > 0.f ? 1.f : 0.2f) * 1.4142135623730951f; }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
-    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+    // no "memory" clobber: nothing in this kernel reads the gradient planes, and a clobber would pin every
+    // texel load behind the previous reduction (one exposed L2 round trip per corner)
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d));
 }
 
 // per-thread weight-gradient accumulators, alive across tiles
@@ -173,19 +175,23 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
             const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
             const int p = __float_as_int(o4.w);
             const float wp = rp[4].x;
+            // per plane: the four texel loads first (independent), then the dot products and reductions
             float fdot = 0.f;  // <dx, f_p> restricted to this lane's channels
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 const float4 w4 = rp[1 + k];
                 const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+                float4 v[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+                    v[c] = (w[c] != 0.f) ? load_feat4<T>(feat, (long long)off[k] + corner[c])
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                 for (int c = 0; c < 4; ++c) {
                     if (w[c] != 0.f) {
-                        const long long e = (long long)off[k] + corner[c];
-                        const float4 v = load_feat4<T>(feat, e);
-                        fdot = fmaf(w[c], v.x * dx.x + v.y * dx.y + v.z * dx.z + v.w * dx.w, fdot);
+                        fdot = fmaf(w[c], v[c].x * dx.x + v[c].y * dx.y + v[c].z * dx.z + v[c].w * dx.w, fdot);
                         const float s_ = w[c] * wp;
-                        red_add_v4(dfeat + e, s_ * dx.x, s_ * dx.y, s_ * dx.z, s_ * dx.w);
+                        red_add_v4(dfeat + (long long)off[k] + corner[c], s_ * dx.x, s_ * dx.y, s_ * dx.z, s_ * dx.w);
                     }
                 }
             }
@@ -325,47 +331,32 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
             __syncthreads();
             decoder_layer<HID, W2S>(s.A1, s.dec.w2, s.dec.b2, s.A2, cnt, m);
             __syncthreads();
-            if (tid < cend) {   // head forward + backward, one thread per point (warps 0..3)
-                float g3[4] = {0.f, 0.f, 0.f, 0.f};
-                if (tid < cnt) {
-                    float o3[4];
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) o3[c] = s.dec.b3[c];
-#pragma unroll 4
-                    for (int k = 0; k < HID; k += 4) {
-                        const float x[4] = {s.A2[k * AS + tid], s.A2[(k + 1) * AS + tid], s.A2[(k + 2) * AS + tid],
-                                            s.A2[(k + 3) * AS + tid]};
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            const float4 w = *reinterpret_cast<const float4*>(s.dec.w3 + c * W2S + k);
-                            o3[c] = fmaf(x[0], w.x, o3[c]);
-                            o3[c] = fmaf(x[1], w.y, o3[c]);
-                            o3[c] = fmaf(x[2], w.z, o3[c]);
-                            o3[c] = fmaf(x[3], w.w, o3[c]);
-                        }
+            if (8 * warp < cend) {   // head forward + backward: four lanes per point, lane c owns output c
+                const int pt = tid >> 2, c = tid & 3;
+                float o3[4];
+                head_split4(s.A2, s.dec, pt, c, o3);
+                float g3 = 0.f;
+                if (pt < cnt) {
+                    const float4 gin = s.pg[s.t.list[c0 + pt]];
+                    const float oc = c == 0 ? o3[0] : c == 1 ? o3[1] : c == 2 ? o3[2] : o3[3];
+                    if (c < 3) {   // rgb = tanh(lrelu(o3))
+                        const float y = tanhf(lrelu_s2(oc));
+                        const float gc = c == 0 ? gin.x : c == 1 ? gin.y : gin.z;
+                        g3 = gc * (1.f - y * y) * act_grad(oc);
+                    } else {       // sigma = 10 * MyReLU(lrelu(o3[3]))
+                        const float raw = lrelu_s2(oc);
+                        const float go = 10.f * gin.w;
+                        // MyReLU backward (NeRF/activation.py:12-16): g*[x>=0] + 0.1*g*[x<0]*[g<0]
+                        const float graw = (raw >= 0.f) ? go : (go < 0.f ? 0.1f * go : 0.f);
+                        g3 = graw * act_grad(oc);
                     }
-                    // head: rgb = tanh(lrelu(o3[0:3])), sigma = 10 * MyReLU(lrelu(o3[3]))
-                    const float4 gin = s.pg[s.t.list[c0 + tid]];
-                    const float gc[3] = {gin.x, gin.y, gin.z};
-#pragma unroll
-                    for (int c = 0; c < 3; ++c) {
-                        const float y = tanhf(lrelu_s2(o3[c]));
-                        g3[c] = gc[c] * (1.f - y * y) * act_grad(o3[c]);
-                    }
-                    const float raw = lrelu_s2(o3[3]);
-                    const float go = 10.f * gin.w;
-                    // MyReLU backward (NeRF/activation.py:12-16): g*[x>=0] + 0.1*g*[x<0]*[g<0]
-                    const float graw = (raw >= 0.f) ? go : (go < 0.f ? 0.1f * go : 0.f);
-                    g3[3] = graw * act_grad(o3[3]);
                 }
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    s.G3[c * AS + tid] = g3[c];
-                    float v = g3[c];
-#pragma unroll
-                    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-                    if (lane == 0) atomicAdd(&s.db3[c], v);
-                }
+                s.G3[c * AS + pt] = g3;
+                float v = g3;   // db3[c]: sum over the warp's 8 points (lanes with the same c)
+                v += __shfl_xor_sync(0xffffffffu, v, 4);
+                v += __shfl_xor_sync(0xffffffffu, v, 8);
+                v += __shfl_xor_sync(0xffffffffu, v, 16);
+                if (lane < 4) atomicAdd(&s.db3[c], v);
             }
             __syncthreads();
             if (tile_on) {   // G2 = (W3^T g3) * act'(a2), in place over A2; dW3 partial sums

@@ -36,51 +36,48 @@ struct __align__(16) FwdSmem {
     float part[ENARF_MAX_PARTS * PART_STRIDE];
     TileSmem t;
     RecSmem r;
-    float X[FEAT * AS];
+    float X[2][FEAT * AS];   // double buffer between the gather warps and the decoder warps
     float A1[HID * AS];
     float A2[HID * AS];
     float4 out[TP_MAX];   // r, g, b, sigma per point (coarse: .x is reused for the alpha weight)
 };
 
-// One decoder layer over the chunk: dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2
+// Warp roles inside a tile's chunk loop: warps 0..7 set up pair records and gather features (latency bound,
+// L2 traffic), warps 8..15 run the decoder GEMMs (FP32 pipe) on the previous chunk; X is double buffered and
+// handed over with named barriers, so the two halves of the CTA overlap instead of alternating.
+#define NG 256                 // gather threads (warps 0..7)
+#define NM 256                 // decoder threads (warps 8..15)
+enum { BAR_G = 1, BAR_M = 2, BAR_FULL0 = 3, BAR_EMPTY0 = 5 };   // FULL0/1 = 3,4  EMPTY0/1 = 5,6
+
+// One decoder layer over the chunk by the 256 decoder threads, 8 points x 4 outputs per thread:
+// dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2
 template <int K, int WS>
 __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, const float* bias, float* dst, int cnt,
-                                              int tid) {
-    const int warp = tid >> 5, lane = tid & 31;
-    const int pqb = warp & 3;
-    if (32 * pqb >= cnt) return;
-    const int pq = pqb * 8 + (lane & 7), og = (warp >> 2) * 4 + (lane >> 3);
-    float acc[4][4];
+                                              int mt) {
+    const int wm = mt >> 5, lane = mt & 31;
+    const int p0 = 64 * (wm & 1);              // this warp's 64 points
+    if (p0 >= cnt) return;
+    const bool two = p0 + 32 < cnt;
+    const int q0 = (wm & 1) * 16 + (lane & 7), q1 = q0 + 8, og = (wm >> 1) * 4 + (lane >> 3);
+    float acc[2][4][4];
 #pragma unroll
-    for (int p = 0; p < 4; ++p)
+    for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[p][j] = 0.f;
-    gemm_kvec<K, WS>(src, Wm, pq, og, acc);
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[h][p][j] = 0.f;
+    gemm_kvec2<K, WS>(src, Wm, q0, q1, two, og, acc);
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
         const int o = og + 16 * j;
         const float bo = bias[o];
-        *reinterpret_cast<float4*>(dst + o * AS + 4 * pq) =
-            make_float4(lrelu_s2(acc[0][j] + bo), lrelu_s2(acc[1][j] + bo), lrelu_s2(acc[2][j] + bo),
-                        lrelu_s2(acc[3][j] + bo));
-    }
-}
-
-// Last layer for the point in column pt: o3[c] = sum_k A2[k][pt] W3[c][k] + b3[c]
-__device__ __forceinline__ void decoder_head(const float* A2, const DecoderSmem& d, int pt, float (&o3)[4]) {
-#pragma unroll
-    for (int c = 0; c < 4; ++c) o3[c] = d.b3[c];
-#pragma unroll 4
-    for (int k = 0; k < HID; k += 4) {
-        const float a[4] = {A2[k * AS + pt], A2[(k + 1) * AS + pt], A2[(k + 2) * AS + pt], A2[(k + 3) * AS + pt]};
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const float4 w = *reinterpret_cast<const float4*>(d.w3 + c * W2S + k);
-            o3[c] = fmaf(a[0], w.x, o3[c]);
-            o3[c] = fmaf(a[1], w.y, o3[c]);
-            o3[c] = fmaf(a[2], w.z, o3[c]);
-            o3[c] = fmaf(a[3], w.w, o3[c]);
-        }
+        *reinterpret_cast<float4*>(dst + o * AS + 4 * q0) =
+            make_float4(lrelu_s2(acc[0][0][j] + bo), lrelu_s2(acc[0][1][j] + bo), lrelu_s2(acc[0][2][j] + bo),
+                        lrelu_s2(acc[0][3][j] + bo));
+        if (two)
+            *reinterpret_cast<float4*>(dst + o * AS + 4 * q1) =
+                make_float4(lrelu_s2(acc[1][0][j] + bo), lrelu_s2(acc[1][1][j] + bo), lrelu_s2(acc[1][2][j] + bo),
+                            lrelu_s2(acc[1][3][j] + bo));
     }
 }
 
@@ -114,26 +111,49 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
         tile_points<MODE>(s.t, s.r, s.part, a.g, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
 
-        // ---- chunks: setup -> gather -> decoder ------------------------------------------------------
-        for (int c0 = 0; c0 < n_active;) {
-            const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
-            setup_pairs<true>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
-            __syncthreads();
-            gather_chunk<T, false>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
-            __syncthreads();
-            decoder_layer<FEAT, W1S>(s.X, s.dec.w1, s.dec.b1, s.A1, cnt, tid);
-            __syncthreads();
-            decoder_layer<HID, W2S>(s.A1, s.dec.w2, s.dec.b2, s.A2, cnt, tid);
-            __syncthreads();
-            if (tid < cnt) {
-                float o3[4];
-                decoder_head(s.A2, s.dec, tid, o3);
-                // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl. the
-                // last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318)
-                s.out[s.t.list[c0 + tid]] = make_float4(tanhf(lrelu_s2(o3[0])), tanhf(lrelu_s2(o3[1])),
-                                                        tanhf(lrelu_s2(o3[2])), fmaxf(lrelu_s2(o3[3]), 0.f) * 10.f);
+        // ---- chunks: gather warps produce X[i & 1], decoder warps consume it ---------------------------
+        if (warp < NG / 32) {
+            int i = 0;
+            for (int c0 = 0; c0 < n_active; ++i) {
+                const int c1 = chunk_end(s.t, c0);
+                setup_pairs<true>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid, NG);
+                bar_sync(BAR_G, NG);
+                if (i >= 2) bar_sync(BAR_EMPTY0 + (i & 1), NG + NM);   // decoder is done with this X buffer
+                gather_chunk<T, false>(s.t, s.r.rec, s.X[i & 1], sc, b, c0, c1, tid, NG);
+                bar_arrive(BAR_FULL0 + (i & 1), NG + NM);
+                bar_sync(BAR_G, NG);                                    // records are free for the next chunk
+                c0 = c1;
             }
-            c0 = c1;
+        } else {
+            const int mt = tid - NG, wm = mt >> 5;
+            int i = 0;
+            for (int c0 = 0; c0 < n_active; ++i) {
+                const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
+                bar_sync(BAR_FULL0 + (i & 1), NG + NM);
+                decoder_layer<FEAT, W1S>(s.X[i & 1], s.dec.w1, s.dec.b1, s.A1, cnt, mt);
+                // hand the X buffer back iff chunk i + 2 exists (the gather warps wait for it exactly then)
+                if (c1 < n_active && chunk_end(s.t, c1) < n_active) bar_arrive(BAR_EMPTY0 + (i & 1), NG + NM);
+                bar_sync(BAR_M, NM);
+                decoder_layer<HID, W2S>(s.A1, s.dec.w2, s.dec.b2, s.A2, cnt, mt);
+                bar_sync(BAR_M, NM);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {   // head: four lanes per point, 64 points per pass
+                    if (64 * h + 8 * wm < cnt) {
+                        const int pt = 64 * h + (mt >> 2);
+                        float o3[4];
+                        head_split4(s.A2, s.dec, pt, mt & 3, o3);
+                        // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl.
+                        // the last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318)
+                        if (pt < cnt) {   // lane c finishes and stores output c
+                            const int c = mt & 3;
+                            const float oc = lrelu_s2(c == 0 ? o3[0] : c == 1 ? o3[1] : c == 2 ? o3[2] : o3[3]);
+                            const float val = c < 3 ? tanhf(oc) : fmaxf(oc, 0.f) * 10.f;
+                            reinterpret_cast<float*>(&s.out[s.t.list[c0 + pt]])[c] = val;
+                        }
+                    }
+                }
+                c0 = c1;
+            }
         }
         __syncthreads();
 

@@ -45,6 +45,7 @@ struct __align__(16) DecoderSmem {
     float w3[4 * W2S];     // [c][o]
     float b1[HID], b2[HID], b3[4];
     float pad_[12];
+    float w3t[HID * 4];    // [o][c]: all four head weights of one hidden unit in one 128-bit load
 };
 
 struct __align__(16) TileSmem {
@@ -71,7 +72,10 @@ __device__ __forceinline__ void load_decoder_smem(DecoderSmem& d, const enarf_sc
     const float* w3 = sc.w3 + (size_t)b * 4 * HID;
     for (int e = tid; e < HID * FEAT; e += NT) d.w1[(e / FEAT) * W1S + (e % FEAT)] = w1[e];
     for (int e = tid; e < HID * HID; e += NT) d.w2[(e / HID) * W2S + (e % HID)] = w2[e];
-    for (int e = tid; e < 4 * HID; e += NT) d.w3[(e / HID) * W2S + (e % HID)] = w3[e];
+    for (int e = tid; e < 4 * HID; e += NT) {
+        d.w3[(e / HID) * W2S + (e % HID)] = w3[e];
+        d.w3t[(e % HID) * 4 + e / HID] = w3[e];
+    }
     if (tid < HID) {
         d.b1[tid] = sc.b1[tid];
         d.b2[tid] = sc.b2[tid];
@@ -224,11 +228,11 @@ __device__ __forceinline__ int chunk_end(const TileSmem& t, int a) {
 // PREMUL: store bilinear weights already multiplied by the part weight (forward); otherwise raw (backward).
 template <bool PREMUL>
 __device__ __forceinline__ void setup_pairs(const TileSmem& t, float* rec, const float* s_part, const enarf_scene_t& sc,
-                                            int b, int a, int e, int tid) {
+                                            int b, int a, int e, int tid, int nthr = NT) {
     const int p0 = t.pref[a], npairs = t.pref[e] - p0;
     const int H = sc.H, W = sc.W;
     const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
-    for (int r = tid; r < npairs; r += NT) {
+    for (int r = tid; r < npairs; r += nthr) {
         const int target = p0 + r;
         int lo = a, hi = e;   // largest q in [a, e) with pref[q] <= target
         while (hi - lo > 1) {
@@ -266,12 +270,12 @@ __device__ __forceinline__ void setup_pairs(const TileSmem& t, float* rec, const
 // SCALE: multiply the stored weights by the part weight on the fly (records hold raw weights).
 template <typename T, bool SCALE>
 __device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec, float* X, const enarf_scene_t& sc,
-                                             int b, int a, int e, int tid) {
+                                             int b, int a, int e, int tid, int nthr = NT) {
     const int lane8 = tid & 7, cnt = e - a, p0 = t.pref[a];
     const int W = sc.W;
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * sc.H * W * FEAT + lane8 * 4;
     const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
-    for (int q = tid >> 3; q < cnt; q += NT / 8) {
+    for (int q = tid >> 3; q < cnt; q += nthr / 8) {
         float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
         const int r1 = t.pref[a + q + 1] - p0;
         for (int r = t.pref[a + q] - p0; r < r1; ++r) {
@@ -303,7 +307,7 @@ __device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec
     }
     // columns [cnt, roundup32(cnt)) feed the decoder tiles of the last partially filled warp: keep them finite
     const int cend = (cnt + 31) & ~31;
-    for (int i = tid; i < FEAT * (cend - cnt); i += NT) {
+    for (int i = tid; i < FEAT * (cend - cnt); i += nthr) {
         const int row = i / (cend - cnt), col = cnt + i - row * (cend - cnt);
         X[row * AS + col] = 0.f;
     }
@@ -384,6 +388,80 @@ __device__ __forceinline__ void wgrad_tile(const float* __restrict__ G, const fl
                 acc[j][jj] = s;
             }
             if (it == 0) bsum[j] += (g[j].x + g[j].y) + (g[j].z + g[j].w);
+        }
+    }
+}
+
+// Decoder head (64 -> 4) with four lanes per point: lane kq sums the hidden units kq, kq+4, ...; after two
+// shuffles every one of the four lanes holds o3[c] = sum_k A2[k][pt] W3[c][k] + b3[c].  All 32 lanes of the
+// warp must call it (points 8*warp .. 8*warp+7).
+__device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& d, int pt, int kq, float (&o3)[4]) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) o3[c] = 0.f;
+#pragma unroll 4
+    for (int i = 0; i < HID / 4; ++i) {
+        const int k = kq + 4 * i;
+        const float x = A2[k * AS + pt];
+        const float4 w = *reinterpret_cast<const float4*>(d.w3t + k * 4);
+        o3[0] = fmaf(x, w.x, o3[0]);
+        o3[1] = fmaf(x, w.y, o3[1]);
+        o3[2] = fmaf(x, w.z, o3[2]);
+        o3[3] = fmaf(x, w.w, o3[3]);
+    }
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 1);
+        o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 2);
+        o3[c] += d.b3[c];
+    }
+}
+
+// ---- named barriers (id 0 is __syncthreads) -------------------------------------------------------------
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(int id, int nthreads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// (1b) as gemm_kvec but 8 points per thread: quads q0 and q1 (q1 skipped when !two); acc[2][4][4] = [quad][p][j]
+template <int K, int WS>
+__device__ __forceinline__ void gemm_kvec2(const float* __restrict__ act, const float* __restrict__ Wm, int q0, int q1,
+                                           bool two, int og, float (&acc)[2][4][4]) {
+#pragma unroll 2
+    for (int k = 0; k < K; k += 4) {
+        float4 w[4], x[4], y[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) w[j] = *reinterpret_cast<const float4*>(Wm + (og + 16 * j) * WS + k);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * q0);
+        if (two) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) y[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * q1);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                acc[0][0][j] = fmaf(x[i].x, wj[i], acc[0][0][j]);
+                acc[0][1][j] = fmaf(x[i].y, wj[i], acc[0][1][j]);
+                acc[0][2][j] = fmaf(x[i].z, wj[i], acc[0][2][j]);
+                acc[0][3][j] = fmaf(x[i].w, wj[i], acc[0][3][j]);
+            }
+        }
+        if (two) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    acc[1][0][j] = fmaf(y[i].x, wj[i], acc[1][0][j]);
+                    acc[1][1][j] = fmaf(y[i].y, wj[i], acc[1][1][j]);
+                    acc[1][2][j] = fmaf(y[i].z, wj[i], acc[1][2][j]);
+                    acc[1][3][j] = fmaf(y[i].w, wj[i], acc[1][3][j]);
+                }
+            }
         }
     }
 }
