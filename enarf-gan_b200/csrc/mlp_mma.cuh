@@ -1,0 +1,172 @@
+// Decoder MLP (32 -> 64 -> 64 -> 4) for 32 points per warp on the tensor pipe, activations chained through
+// registers.  Replaces libraries/NeRF/net.py:10-27 (StyledMLP) applied point-wise
+// (libraries/triplane/triplane_nerf.py:44-47) with W_eff / bias supplied per sample.
+//
+// Precision: the parity bar is 1e-4 on fp32 outputs, so every product is the error-compensated 3xTF32 form
+//   a*b ~= hi(a)*hi(b) + hi(a)*lo(b) + lo(a)*hi(b),   hi(x) = x with the low 13 mantissa bits cleared, lo = x - hi
+// (the dropped lo*lo term is ~2^-22 relative), accumulated in fp32 by mma.sync.m16n8k8.tf32.  Measured issue
+// rate on B200: 139 TMAC/s (profiles/mma_rate_r1.txt) -> 46 TMAC/s effective, above the 36 TMAC/s FFMA peak,
+// and -- the real point -- it takes the decoder off the FMA / shared-memory pipes that the gather needs: the
+// FFMA version was bound by LDS wavefronts (2-4 per 128-bit request, profiles/ncu_summary_r1_v3.txt).
+//
+// Register chaining: the m16n8 accumulator fragment (c0,c1 = row g, cols 2t,2t+1; c2,c3 = row g+8) is used
+// directly as the A fragment of the next layer's k-block by choosing the k permutation
+//   logical k = t  <->  channel 8j+2t,   logical k = t+4  <->  channel 8j+2t+1
+// and loading the B fragment (weights) with the same permutation: one 64-bit load W[n][8j+2t .. 8j+2t+1].
+// Layer 2's output is consumed n-tile by n-tile as k-blocks of layer 3, so it never materialises.
+#pragma once
+#include "common.cuh"
+#include "gather.cuh"
+
+#define XS 40    // row stride (floats) of the per-warp feature slab X[point][channel]: 8g + 2t covers 32 banks
+#define W1M 40   // weight row strides for the 64-bit B-fragment loads (same bank argument)
+#define W2M 72
+
+struct __align__(16) DecoderMma {
+    float w1[HID * W1M];   // [o][i]
+    float w2[HID * W2M];   // [o][i]
+    float w3[8 * W2M];     // [c][o], rows 4..7 zero
+    float b1[HID], b2[HID], b3[8];
+};
+
+__device__ __forceinline__ void load_decoder_mma(DecoderMma& d, const enarf_scene_t& sc, int b, int tid, int nthr) {
+    const float* w1 = sc.w1 + (size_t)b * HID * FEAT;
+    const float* w2 = sc.w2 + (size_t)b * HID * HID;
+    const float* w3 = sc.w3 + (size_t)b * 4 * HID;
+    for (int e = tid; e < HID * FEAT; e += nthr) d.w1[(e / FEAT) * W1M + (e % FEAT)] = w1[e];
+    for (int e = tid; e < HID * HID; e += nthr) d.w2[(e / HID) * W2M + (e % HID)] = w2[e];
+    for (int e = tid; e < 8 * HID; e += nthr) d.w3[(e / HID) * W2M + (e % HID)] = (e < 4 * HID) ? w3[e] : 0.f;
+    for (int e = tid; e < HID; e += nthr) {
+        d.b1[e] = sc.b1[e];
+        d.b2[e] = sc.b2[e];
+    }
+    if (tid < 8) d.b3[tid] = tid < 4 ? sc.b3[tid] : 0.f;
+}
+
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+__device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
+}
+
+// One k-block of one 16-row tile against one n-tile: main += hi*hi, small += lo*hi + hi*lo
+__device__ __forceinline__ void mma3(float (&main)[4], float (&small)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4],
+                                     uint32_t bh0, uint32_t bh1, uint32_t bl0, uint32_t bl1) {
+    mma_tf32(small, al, bh0, bh1);
+    mma_tf32(small, ah, bl0, bl1);
+    mma_tf32(main, ah, bh0, bh1);
+}
+
+// X: this warp's slab [32 points][XS] (rows of points it does not own may hold anything finite or not: a row
+// only influences its own outputs).  Returns the head's pre-activation outputs as accumulator fragments:
+// o3[mt][0] = (point 16mt+g,   channel 2t)   o3[mt][1] = (point 16mt+g,   channel 2t+1)
+// o3[mt][2] = (point 16mt+g+8, channel 2t)   o3[mt][3] = (point 16mt+g+8, channel 2t+1);  channels >= 4 are padding.
+__device__ __forceinline__ void decode32_mma(const float* __restrict__ X, const DecoderMma& d, int lane,
+                                             float (&o3)[2][4]) {
+    const int g = lane >> 2, t = lane & 3;
+    float acc1[2][8][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc1[mt][nt][i] = 0.f;
+
+    // ---- layer 1: 32 -> 64 -------------------------------------------------------------------------------
+#pragma unroll 1
+    for (int j = 0; j < FEAT / 8; ++j) {
+        uint32_t ah[2][4], al[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            const float2 v0 = *reinterpret_cast<const float2*>(X + (16 * mt + g) * XS + 8 * j + 2 * t);
+            const float2 v1 = *reinterpret_cast<const float2*>(X + (16 * mt + g + 8) * XS + 8 * j + 2 * t);
+            split_tf32(v0.x, ah[mt][0], al[mt][0]);
+            split_tf32(v1.x, ah[mt][1], al[mt][1]);
+            split_tf32(v0.y, ah[mt][2], al[mt][2]);
+            split_tf32(v1.y, ah[mt][3], al[mt][3]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const float2 w = *reinterpret_cast<const float2*>(d.w1 + (8 * nt + g) * W1M + 8 * j + 2 * t);
+            uint32_t bh0, bl0, bh1, bl1;
+            split_tf32(w.x, bh0, bl0);
+            split_tf32(w.y, bh1, bl1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], al[mt], bh0, bh1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], ah[mt], bl0, bl1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], ah[mt], bh0, bh1);
+        }
+    }
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+        const float2 b = *reinterpret_cast<const float2*>(d.b1 + 8 * nt + 2 * t);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            acc1[mt][nt][0] = lrelu_s2(acc1[mt][nt][0] + b.x);
+            acc1[mt][nt][1] = lrelu_s2(acc1[mt][nt][1] + b.y);
+            acc1[mt][nt][2] = lrelu_s2(acc1[mt][nt][2] + b.x);
+            acc1[mt][nt][3] = lrelu_s2(acc1[mt][nt][3] + b.y);
+        }
+    }
+
+    // ---- layer 2 (64 -> 64) one n-tile at a time, each finished n-tile feeding layer 3 (64 -> 4) as a k-block --
+    float m3[2][4], s3[2][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) m3[mt][i] = s3[mt][i] = 0.f;
+#pragma unroll 1
+    for (int nt = 0; nt < 8; ++nt) {
+        float m2[2][4], s2[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) m2[mt][i] = s2[mt][i] = 0.f;
+        const float* wrow = d.w2 + (8 * nt + g) * W2M + 2 * t;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float2 w = *reinterpret_cast<const float2*>(wrow + 8 * j);
+            uint32_t bh0, bl0, bh1, bl1;
+            split_tf32(w.x, bh0, bl0);
+            split_tf32(w.y, bh1, bl1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) {
+                uint32_t ah[4], al[4];
+                split_tf32(acc1[mt][j][0], ah[0], al[0]);
+                split_tf32(acc1[mt][j][2], ah[1], al[1]);
+                split_tf32(acc1[mt][j][1], ah[2], al[2]);
+                split_tf32(acc1[mt][j][3], ah[3], al[3]);
+                mma3(m2[mt], s2[mt], ah, al, bh0, bh1, bl0, bl1);
+            }
+        }
+        const float2 b = *reinterpret_cast<const float2*>(d.b2 + 8 * nt + 2 * t);
+        const float2 w3 = *reinterpret_cast<const float2*>(d.w3 + g * W2M + 8 * nt + 2 * t);
+        uint32_t bh0, bl0, bh1, bl1;
+        split_tf32(w3.x, bh0, bl0);
+        split_tf32(w3.y, bh1, bl1);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            uint32_t ah[4], al[4];
+            split_tf32(lrelu_s2(m2[mt][0] + s2[mt][0] + b.x), ah[0], al[0]);
+            split_tf32(lrelu_s2(m2[mt][2] + s2[mt][2] + b.x), ah[1], al[1]);
+            split_tf32(lrelu_s2(m2[mt][1] + s2[mt][1] + b.y), ah[2], al[2]);
+            split_tf32(lrelu_s2(m2[mt][3] + s2[mt][3] + b.y), ah[3], al[3]);
+            mma3(m3[mt], s3[mt], ah, al, bh0, bh1, bl0, bl1);
+        }
+    }
+    const float2 b3 = *reinterpret_cast<const float2*>(d.b3 + 2 * t);
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+        o3[mt][0] = m3[mt][0] + s3[mt][0] + b3.x;
+        o3[mt][1] = m3[mt][1] + s3[mt][1] + b3.y;
+        o3[mt][2] = m3[mt][2] + s3[mt][2] + b3.x;
+        o3[mt][3] = m3[mt][3] + s3[mt][3] + b3.y;
+    }
+}

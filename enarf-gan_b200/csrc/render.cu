@@ -3,13 +3,19 @@
 // Reference being replaced: libraries/NeRF/rendering.py:119-335, models/narf.py:147-275,
 // libraries/triplane/sampling.py:54-127, libraries/triplane/triplane_nerf.py:32-48.
 //
-// Tiling, pair records, gather and the register-tiled decoder GEMMs are described in tile.cuh.  Per chunk:
-//   setup -> gather -> L1 (32->64) -> L2 (64->64) -> L3 + head (64->4, one thread per point) ; then per tile
-//   one warp per ray composites: shuffle scan of sigma*delta -> transmittance -> weights -> colour/mask/disparity.
+// One 512-thread CTA per SM owns whole rays (tile.cuh: phase 0/1, compaction, pair prefix).  Inside a tile the
+// 16 warps are autonomous: each pulls chunks of 32 active points from a shared-memory counter and, with no
+// CTA-wide barrier,
+//   sets up the (point, part) pair records of its points (one lane per pair), gathers the features with 8 lanes
+//   per point into its own 5 KB slab, and runs the 32->64->64->4 decoder for its 32 points on the tensor pipe
+//   (mlp_mma.cuh: error-compensated 3xTF32 mma.sync, activations chained through registers),
+// so that the latency-bound gathers of some warps overlap the tensor work of others.  Then one warp per ray
+// composites: shuffle scan of sigma*delta -> transmittance -> weights -> colour/mask/disparity.
 // Per-point features, activations, densities and colours live only in shared memory / registers.  The grid is
-// persistent (one CTA per SM) and pulls tiles in sample-major order from an atomic counter so that one
-// sample's planes stay L2-resident and the decoder weights are reloaded only when the sample changes.
+// persistent and pulls tiles in sample-major order from an atomic counter so that one sample's planes stay
+// L2-resident and the decoder weights are reloaded only when the sample changes.
 #include "tile.cuh"
+#include "mlp_mma.cuh"
 
 enum { MODE_COARSE = TILE_COARSE, MODE_FINE = TILE_FINE, MODE_QUERY = TILE_QUERY };
 
@@ -31,55 +37,22 @@ struct RenderArgs {
     uint32_t* q_mask;
 };
 
-struct __align__(16) FwdSmem {
-    DecoderSmem dec;
-    float part[ENARF_MAX_PARTS * PART_STRIDE];
-    TileSmem t;
-    RecSmem r;
-    float X[2][FEAT * AS];   // double buffer between the gather warps and the decoder warps
-    float A1[HID * AS];
-    float A2[HID * AS];
-    float4 out[TP_MAX];   // r, g, b, sigma per point (coarse: .x is reused for the alpha weight)
+struct __align__(16) WarpSlab {
+    float X[32 * XSW];        // features of the warp's 32 points, [point][channel]
+    float rec[RECW * REC];    // pair records of the current sub-batch
 };
 
-// Warp roles inside a tile's chunk loop: warps 0..7 set up pair records and gather features (latency bound,
-// L2 traffic), warps 8..15 run the decoder GEMMs (FP32 pipe) on the previous chunk; X is double buffered and
-// handed over with named barriers, so the two halves of the CTA overlap instead of alternating.
-#define NG 256                 // gather threads (warps 0..7)
-#define NM 256                 // decoder threads (warps 8..15)
-enum { BAR_G = 1, BAR_M = 2, BAR_FULL0 = 3, BAR_EMPTY0 = 5 };   // FULL0/1 = 3,4  EMPTY0/1 = 5,6
-
-// One decoder layer over the chunk by the 256 decoder threads, 8 points x 4 outputs per thread:
-// dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2
-template <int K, int WS>
-__device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, const float* bias, float* dst, int cnt,
-                                              int mt) {
-    const int wm = mt >> 5, lane = mt & 31;
-    const int p0 = 64 * (wm & 1);              // this warp's 64 points
-    if (p0 >= cnt) return;
-    const bool two = p0 + 32 < cnt;
-    const int q0 = (wm & 1) * 16 + (lane & 7), q1 = q0 + 8, og = (wm >> 1) * 4 + (lane >> 3);
-    float acc[2][4][4];
-#pragma unroll
-    for (int h = 0; h < 2; ++h)
-#pragma unroll
-        for (int p = 0; p < 4; ++p)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) acc[h][p][j] = 0.f;
-    gemm_kvec2<K, WS>(src, Wm, q0, q1, two, og, acc);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int o = og + 16 * j;
-        const float bo = bias[o];
-        *reinterpret_cast<float4*>(dst + o * AS + 4 * q0) =
-            make_float4(lrelu_s2(acc[0][0][j] + bo), lrelu_s2(acc[0][1][j] + bo), lrelu_s2(acc[0][2][j] + bo),
-                        lrelu_s2(acc[0][3][j] + bo));
-        if (two)
-            *reinterpret_cast<float4*>(dst + o * AS + 4 * q1) =
-                make_float4(lrelu_s2(acc[1][0][j] + bo), lrelu_s2(acc[1][1][j] + bo), lrelu_s2(acc[1][2][j] + bo),
-                            lrelu_s2(acc[1][3][j] + bo));
-    }
-}
+struct __align__(16) FwdSmem {
+    DecoderMma dec;
+    float part[ENARF_MAX_PARTS * PART_STRIDE];
+    TileSmem t;
+    float4 out[TP_MAX];       // r, g, b, sigma per point (coarse: .x is reused for the alpha weight)
+    union {
+        WarpSlab slab[NWARP];
+        float cull[MAX_RAYS * ENARF_MAX_PARTS * 2];   // phase 0/1 only (tile_points sees it as RecSmem::cull)
+    } u;
+};
+static_assert(XSW == XS, "gather slab stride must match the decoder's A-fragment loads");
 
 template <int MODE, typename T>
 __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
@@ -103,56 +76,47 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
         const int tp = rays * S;
         if (b != cur_b) {
             load_part_params(s.part, sc, b, tid, NT);
-            load_decoder_smem(s.dec, sc, b, tid);
+            load_decoder_mma(s.dec, sc, b, tid, NT);
             cur_b = b;
         }
         for (int i = tid; i < tp; i += NT) s.out[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tid == 0) s.t.pad_[0] = 0;   // chunk counter of this tile
         __syncthreads();
-        tile_points<MODE>(s.t, s.r, s.part, a.g, sc.P, b, ray0, rays, tid);
+        tile_points<MODE>(s.t, *reinterpret_cast<RecSmem*>(&s.u), s.part, a.g, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
 
-        // ---- chunks: gather warps produce X[i & 1], decoder warps consume it ---------------------------
-        if (warp < NG / 32) {
-            int i = 0;
-            for (int c0 = 0; c0 < n_active; ++i) {
-                const int c1 = chunk_end(s.t, c0);
-                setup_pairs<true>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid, NG);
-                bar_sync(BAR_G, NG);
-                if (i >= 2) bar_sync(BAR_EMPTY0 + (i & 1), NG + NM);   // decoder is done with this X buffer
-                gather_chunk<T, false>(s.t, s.r.rec, s.X[i & 1], sc, b, c0, c1, tid, NG);
-                bar_arrive(BAR_FULL0 + (i & 1), NG + NM);
-                bar_sync(BAR_G, NG);                                    // records are free for the next chunk
-                c0 = c1;
-            }
-        } else {
-            const int mt = tid - NG, wm = mt >> 5;
-            int i = 0;
-            for (int c0 = 0; c0 < n_active; ++i) {
-                const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
-                bar_sync(BAR_FULL0 + (i & 1), NG + NM);
-                decoder_layer<FEAT, W1S>(s.X[i & 1], s.dec.w1, s.dec.b1, s.A1, cnt, mt);
-                // hand the X buffer back iff chunk i + 2 exists (the gather warps wait for it exactly then)
-                if (c1 < n_active && chunk_end(s.t, c1) < n_active) bar_arrive(BAR_EMPTY0 + (i & 1), NG + NM);
-                bar_sync(BAR_M, NM);
-                decoder_layer<HID, W2S>(s.A1, s.dec.w2, s.dec.b2, s.A2, cnt, mt);
-                bar_sync(BAR_M, NM);
+        // ---- chunks of 32 active points, one warp each, no CTA barrier ---------------------------------
+        {
+            WarpSlab& my = s.u.slab[warp];
+            const int g = lane >> 2, t4 = lane & 3;
+            for (;;) {
+                int c = 0;
+                if (lane == 0) c = atomicAdd(&s.t.pad_[0], 1);
+                c = __shfl_sync(0xffffffffu, c, 0);
+                const int a0 = 32 * c;
+                if (a0 >= n_active) break;
+                const int np = min(32, n_active - a0);
+                gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane);
+                float o3[2][4];
+                decode32_mma(my.X, s.dec, lane, o3);
+                __syncwarp();   // every lane is done reading X before the next chunk's gather overwrites it
+                // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl. the
+                // last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318).
+                // Lane (g, t4) holds channels 2*t4, 2*t4+1 of points g and g+8 of each 16-row tile; t4 >= 2 is padding.
+                if (t4 < 2) {
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {   // head: four lanes per point, 64 points per pass
-                    if (64 * h + 8 * wm < cnt) {
-                        const int pt = 64 * h + (mt >> 2);
-                        float o3[4];
-                        head_split4(s.A2, s.dec, pt, mt & 3, o3);
-                        // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl.
-                        // the last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318)
-                        if (pt < cnt) {   // lane c finishes and stores output c
-                            const int c = mt & 3;
-                            const float oc = lrelu_s2(c == 0 ? o3[0] : c == 1 ? o3[1] : c == 2 ? o3[2] : o3[3]);
-                            const float val = c < 3 ? tanhf(oc) : fmaxf(oc, 0.f) * 10.f;
-                            reinterpret_cast<float*>(&s.out[s.t.list[c0 + pt]])[c] = val;
+                    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const int row = 16 * mt + 8 * h + g;
+                            if (row < np) {
+                                const float v0 = lrelu_s2(o3[mt][2 * h]), v1 = lrelu_s2(o3[mt][2 * h + 1]);
+                                const float2 r = t4 == 0 ? make_float2(tanhf(v0), tanhf(v1))
+                                                         : make_float2(tanhf(v0), fmaxf(v1, 0.f) * 10.f);
+                                reinterpret_cast<float2*>(&s.out[s.t.list[a0 + row]])[t4] = r;
+                            }
                         }
-                    }
                 }
-                c0 = c1;
             }
         }
         __syncthreads();

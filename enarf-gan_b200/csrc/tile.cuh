@@ -465,3 +465,83 @@ __device__ __forceinline__ void gemm_kvec2(const float* __restrict__ act, const 
         }
     }
 }
+
+// ---- warp-autonomous gather (forward): one warp owns the 32 active points [a, a+np) of a chunk ----------
+// Records go to the warp's own slab `rec` (RECW records), features to its slab X[point][XSW]; only __syncwarp.
+#define RECW 48     // pair records per warp sub-batch (one point has at most 32 pairs)
+#define XSW 40      // feature slab row stride (see mlp_mma.cuh XS)
+
+template <typename T>
+__device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, float* X, const float* s_part,
+                                              const enarf_scene_t& sc, int b, int a, int np, int lane) {
+    const int H = sc.H, W = sc.W;
+    const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
+    const int lane8 = lane & 7, grp = lane >> 3;
+    const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * H * W * FEAT + lane8 * 4;
+    const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
+    for (int q0 = 0; q0 < np;) {
+        // points [q0, q1) whose pairs fit the record slab
+        const int base = t.pref[a + q0];
+        const int mine = (lane >= q0 && lane < np) ? t.pref[a + lane + 1] - base : (RECW + 1);
+        const int q1 = q0 + __popc(__ballot_sync(0xffffffffu, mine <= RECW));
+        const int npairs = t.pref[a + q1] - base;
+        // ---- setup: one lane per pair ------------------------------------------------------------------
+        for (int r = lane; r < npairs; r += 32) {
+            const int target = base + r;
+            int lo = a + q0, hi = a + q1;   // largest q with pref[q] <= target
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (t.pref[mid] <= target) lo = mid; else hi = mid;
+            }
+            const float4 pm = t.pm[t.list[lo]];
+            uint32_t m = __float_as_uint(pm.w);
+            for (int k = target - t.pref[lo]; k > 0; --k) m &= m - 1;
+            const int p = __ffs(m) - 1;
+            float c[3];
+            part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
+            Bilin bl[3];
+            float wp = 1.f;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
+                wp *= sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
+            }
+            float4* dst = reinterpret_cast<float4*>(rec + r * REC);
+            dst[0] = make_float4(__int_as_float((bl[0].y0 * W + bl[0].x0) * FEAT),
+                                 __int_as_float((H * W + bl[1].y0 * W + bl[1].x0) * FEAT),
+                                 __int_as_float((2 * H * W + bl[2].y0 * W + bl[2].x0) * FEAT), __int_as_float(p));
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                dst[1 + k] = make_float4(bl[k].w00 * wp, bl[k].w01 * wp, bl[k].w10 * wp, bl[k].w11 * wp);
+        }
+        __syncwarp();
+        // ---- gather: 8 lanes per point, the four groups take points q0+grp, q0+grp+4, ... ---------------
+        for (int q = q0 + grp; q < q1; q += 4) {
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+            const int r1 = t.pref[a + q + 1] - base;
+            for (int r = t.pref[a + q] - base; r < r1; ++r) {
+                const float4* rp = reinterpret_cast<const float4*>(rec + r * REC);
+                const float4 o4 = rp[0];
+                const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float4 w4 = rp[1 + k];
+                    const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        if (w[c] != 0.f) {
+                            const float4 v = load_feat4<T>(feat, (long long)off[k] + corner[c]);
+                            f.x = fmaf(w[c], v.x, f.x);
+                            f.y = fmaf(w[c], v.y, f.y);
+                            f.z = fmaf(w[c], v.z, f.z);
+                            f.w = fmaf(w[c], v.w, f.w);
+                        }
+                    }
+                }
+            }
+            *reinterpret_cast<float4*>(X + q * XSW + 4 * lane8) = f;
+        }
+        __syncwarp();
+        q0 = q1;
+    }
+}
