@@ -152,61 +152,60 @@ __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm,
     }
 }
 
-// Scatter for the chunk [c0, c1): 8 lanes per point, lane l owns channels 4l..4l+3 of dX (rows of X).
+// Scatter for the chunk [c0, c1): 8 lanes per (point, part) PAIR -- pairs are independent here, so the work
+// is spread evenly over the 64 groups whatever the number of parts per point; lane l owns channels 4l..4l+3.
 template <typename T>
 __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* rec, const float* X, const BwdArgs& a,
                                               int b, int c0, int c1, int tid) {
     const enarf_scene_t& sc = a.sc;
-    const int lane8 = tid & 7, cnt = c1 - c0, p0 = t.pref[c0];
+    const int lane8 = tid & 7, npairs = t.pref[c1] - t.pref[c0];
     const int H = sc.H, W = sc.W, HW = H * W;
     const unsigned gmask = 0xffu << (tid & 24);
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dfeat = a.d_feat + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dprob = a.d_prob + (size_t)b * a.d_prob_stride;
     const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
-    for (int q = tid >> 3; q < cnt; q += NT / 8) {
+    for (int r = tid >> 3; r < npairs; r += NT / 8) {
+        const float* rw = rec + r * REC;
+        const float4* rp = reinterpret_cast<const float4*>(rw);
+        const float4 o4 = rp[0];
+        const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+        const int p = __float_as_int(o4.w) & 255, q = __float_as_int(o4.w) >> 8;
+        const float wp = rp[4].x;
+        float w[12];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float4 w4 = rp[1 + k];
+            w[4 * k] = w4.x; w[4 * k + 1] = w4.y; w[4 * k + 2] = w4.z; w[4 * k + 3] = w4.w;
+        }
+        // all texel loads first (independent), then the dot products and the reductions
+        float4 v[12];
+#pragma unroll
+        for (int e = 0; e < 12; ++e)
+            v[e] = (w[e] != 0.f) ? load_feat4<T>(feat, (long long)off[e >> 2] + corner[e & 3])
+                                 : make_float4(0.f, 0.f, 0.f, 0.f);
         const float* src = X + (lane8 * 4) * AS + q;
         const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
-        const int r1 = t.pref[c0 + q + 1] - p0;
-        for (int r = t.pref[c0 + q] - p0; r < r1; ++r) {
-            const float* rw = rec + r * REC;
-            const float4* rp = reinterpret_cast<const float4*>(rw);
-            const float4 o4 = rp[0];
-            const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
-            const int p = __float_as_int(o4.w);
-            const float wp = rp[4].x;
-            // per plane: the four texel loads first (independent), then the dot products and reductions
-            float fdot = 0.f;  // <dx, f_p> restricted to this lane's channels
+        float fdot = 0.f;  // <dx, f_p> restricted to this lane's channels
 #pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float4 w4 = rp[1 + k];
-                const float w[4] = {w4.x, w4.y, w4.z, w4.w};
-                float4 v[4];
-#pragma unroll
-                for (int c = 0; c < 4; ++c)
-                    v[c] = (w[c] != 0.f) ? load_feat4<T>(feat, (long long)off[k] + corner[c])
-                                         : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    if (w[c] != 0.f) {
-                        fdot = fmaf(w[c], v[c].x * dx.x + v[c].y * dx.y + v[c].z * dx.z + v[c].w * dx.w, fdot);
-                        const float s_ = w[c] * wp;
-                        red_add_v4(dfeat + (long long)off[k] + corner[c], s_ * dx.x, s_ * dx.y, s_ * dx.z, s_ * dx.w);
-                    }
-                }
+        for (int e = 0; e < 12; ++e) {
+            if (w[e] != 0.f) {
+                fdot = fmaf(w[e], v[e].x * dx.x + v[e].y * dx.y + v[e].z * dx.z + v[e].w * dx.w, fdot);
+                const float s_ = w[e] * wp;
+                red_add_v4(dfeat + (long long)off[e >> 2] + corner[e & 3], s_ * dx.x, s_ * dx.y, s_ * dx.z, s_ * dx.w);
             }
-            fdot += __shfl_xor_sync(gmask, fdot, 1);
-            fdot += __shfl_xor_sync(gmask, fdot, 2);
-            fdot += __shfl_xor_sync(gmask, fdot, 4);
-            // d w_p = fdot;  w_p = prod sigmoid(v_k)  ->  d v_k = fdot * w_p * (1 - sigmoid(v_k))
-            for (int e = lane8; e < 12; e += 8) {
-                const int k = e >> 2, c = e & 3;
-                const float bw = rw[4 + e];
-                if (bw != 0.f) {
-                    const float dv = fdot * wp * (1.f - rw[17 + k]);
-                    const int pix = (off[k] >> 5) - k * HW + (c >> 1) * W + (c & 1);
-                    atomicAdd(dprob + (size_t)(3 * p + k) * HW + pix, bw * dv);
-                }
+        }
+        fdot += __shfl_xor_sync(gmask, fdot, 1);
+        fdot += __shfl_xor_sync(gmask, fdot, 2);
+        fdot += __shfl_xor_sync(gmask, fdot, 4);
+        // d w_p = fdot;  w_p = prod sigmoid(v_k)  ->  d v_k = fdot * w_p * (1 - sigmoid(v_k))
+        for (int e = lane8; e < 12; e += 8) {
+            const int k = e >> 2, c = e & 3;
+            const float bw = rw[4 + e];
+            if (bw != 0.f) {
+                const float dv = fdot * wp * (1.f - rw[17 + k]);
+                const int pix = (off[k] >> 5) - k * HW + (c >> 1) * W + (c & 1);
+                atomicAdd(dprob + (size_t)(3 * p + k) * HW + pix, bw * dv);
             }
         }
     }

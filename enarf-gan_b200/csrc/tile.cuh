@@ -37,7 +37,7 @@
 static_assert(TP_MAX == 2 * NT, "the prefix scan handles two list entries per thread");
 
 // record layout (words): 0..2 element offset of texel (y0,x0) of plane k inside the sample's feature planes,
-// 3 part id, 4..15 bilinear weights [k][corner] (forward: already multiplied by the part weight),
+// 3 part id | point slot << 8, 4..15 bilinear weights [k][corner] (forward: already multiplied by the part weight),
 // 16 part weight wp = prod sigmoid, 17..19 sigmoid(prob sample k)
 struct __align__(16) DecoderSmem {
     float w1[HID * W1S];   // [o][i]
@@ -258,7 +258,9 @@ __device__ __forceinline__ void setup_pairs(const TileSmem& t, float* rec, const
         int off[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) off[k] = (k * H * W + bl[k].y0 * W + bl[k].x0) * FEAT;
-        dst[0] = make_float4(__int_as_float(off[0]), __int_as_float(off[1]), __int_as_float(off[2]), __int_as_float(p));
+        // word 3: part id | (point slot within the chunk << 8)
+        dst[0] = make_float4(__int_as_float(off[0]), __int_as_float(off[1]), __int_as_float(off[2]),
+                             __int_as_float(p | ((lo - a) << 8)));
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             dst[1 + k] = make_float4(bl[k].w00 * ws, bl[k].w01 * ws, bl[k].w10 * ws, bl[k].w11 * ws);
