@@ -16,6 +16,7 @@
 //      gradient planes using the same pair records; d(part weight) goes through the sigmoid product into
 //      scalar reductions on the probability planes.
 #include "tile.cuh"
+#include "mma_smem.cuh"
 
 struct BwdArgs {
     enarf_scene_t sc;
@@ -35,6 +36,8 @@ struct BwdArgs {
 
 struct __align__(16) BwdSmem {
     DecoderSmem dec;
+    float w2t[HID * W2S];    // [i][o]  W2 transposed: B fragments of G1 = G2 W2
+    float w1t[FEAT * W2S];   // [c][o]  W1 transposed: B fragments of dX = G1 W1
     float part[ENARF_MAX_PARTS * PART_STRIDE];
     TileSmem t;
     RecSmem r;
@@ -57,26 +60,29 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 
 // per-thread weight-gradient accumulators, alive across tiles
 struct WGrad {
-    float w2[4][4];   // rows ot + 16 j, cols it + 16 jj, point quads q = h mod 2
-    float w1[4][4];   // rows ot + 16 j, cols it + 8 jj,  point quads q = h mod 4
-    float w3[4][4];   // [c][j]: row c, col og + 16 j, this thread's point quad
-    float b2[4], b1[4];
+    float w2[1][2][4];   // mma tiles: rows (o) 16*(warp&3)+g(+8), cols (i) 16*(warp>>2) + 8 nt + 2t(+1)
+    float w1[1][1][4];   // rows (o) 16*(warp&3)+g(+8), cols (c) 8*(warp>>2) + 2t(+1)
+    float w3[4][4];      // [c][j]: row c, col og + 16 j, summed over this thread's point quad
+    float b2[4];         // cols og + 16 j, this thread's point quad
+    float b1[2][2];      // cols 16*(warp>>2) + 8 nt + 2t + {0,1}, this lane's rows
 };
 
 __device__ __forceinline__ void wgrad_zero(WGrad& g) {
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) g.w2[i][j] = g.w1[i][j] = g.w3[i][j] = 0.f;
-        g.b2[i] = g.b1[i] = 0.f;
+        for (int j = 0; j < 4; ++j) g.w3[i][j] = 0.f;
+        g.w2[0][0][i] = g.w2[0][1][i] = g.w1[0][0][i] = 0.f;
+        g.b2[i] = 0.f;
     }
+    g.b1[0][0] = g.b1[0][1] = g.b1[1][0] = g.b1[1][1] = 0.f;
 }
 
-// thread -> tile coordinates of the three mappings (see tile.cuh for the bank argument)
+// thread -> tile coordinates: (pq, og) for the element-wise FP32 passes (4 points x outs og+16j),
+// (pb, ob, g, t) for the mma phases (warp tile: 32 points x 16 outs, or one/two weight-gradient tiles)
 struct Maps {
-    int pq, og;          // decoder tiles: point quad, out group (also in group of the dgrad GEMMs)
-    int ot2, it2, h2;    // dW2
-    int ot1, it1, h1;    // dW1
+    int pq, og;
+    int pb, ob, g, t;
 };
 
 __device__ __forceinline__ Maps make_maps(int tid) {
@@ -84,71 +90,88 @@ __device__ __forceinline__ Maps make_maps(int tid) {
     Maps m;
     m.pq = (w & 3) * 8 + (lane & 7);
     m.og = (w >> 2) * 4 + (lane >> 3);
-    m.h2 = w & 1;
-    m.ot2 = ((w >> 1) & 1) * 8 + (lane & 7);
-    m.it2 = (w >> 2) * 4 + (lane >> 3);
-    m.h1 = w & 3;
-    m.ot1 = ((w >> 2) & 1) * 8 + (lane & 7);
-    m.it1 = (w >> 3) * 4 + (lane >> 3);
+    m.pb = w & 3;
+    m.ob = w >> 2;
+    m.g = lane >> 2;
+    m.t = lane & 3;
     return m;
 }
 
-__device__ __forceinline__ void wgrad_flush(WGrad& g, const Maps& m, float* db3s, const BwdArgs& a, int b, int tid) {
+__device__ __forceinline__ void wgrad_flush(WGrad& wg, const Maps& m, float* db3s, const BwdArgs& a, int b, int tid) {
     float* d1 = a.d_w1 + (size_t)b * HID * FEAT;
     float* d2 = a.d_w2 + (size_t)b * HID * HID;
     float* d3 = a.d_w3 + (size_t)b * 4 * HID;
+    const int r0 = 16 * m.pb + m.g;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int nt = 0; nt < 2; ++nt) {
+        const int c = 16 * m.ob + 8 * nt + 2 * m.t;
+        atomicAdd(d2 + r0 * HID + c, wg.w2[0][nt][0]);
+        atomicAdd(d2 + r0 * HID + c + 1, wg.w2[0][nt][1]);
+        atomicAdd(d2 + (r0 + 8) * HID + c, wg.w2[0][nt][2]);
+        atomicAdd(d2 + (r0 + 8) * HID + c + 1, wg.w2[0][nt][3]);
+    }
+    {
+        const int c = 8 * m.ob + 2 * m.t;
+        atomicAdd(d1 + r0 * FEAT + c, wg.w1[0][0][0]);
+        atomicAdd(d1 + r0 * FEAT + c + 1, wg.w1[0][0][1]);
+        atomicAdd(d1 + (r0 + 8) * FEAT + c, wg.w1[0][0][2]);
+        atomicAdd(d1 + (r0 + 8) * FEAT + c + 1, wg.w1[0][0][3]);
+    }
+    // dW3 / db2: the 8 lanes that share an out group hold partial sums over different point quads
 #pragma unroll
-        for (int jj = 0; jj < 4; ++jj) {
-            atomicAdd(d2 + (m.ot2 + 16 * j) * HID + m.it2 + 16 * jj, g.w2[j][jj]);
-            atomicAdd(d1 + (m.ot1 + 16 * j) * FEAT + m.it1 + 8 * jj, g.w1[j][jj]);
-        }
-    // dW3: the 8 lanes that share an out group hold partial sums over different point quads
+    for (int j = 0; j < 4; ++j) {
 #pragma unroll
-    for (int c = 0; c < 4; ++c)
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            float v = g.w3[c][j];
+        for (int c = 0; c < 4; ++c) {
+            float v = wg.w3[c][j];
             v += __shfl_xor_sync(0xffffffffu, v, 1);
             v += __shfl_xor_sync(0xffffffffu, v, 2);
             v += __shfl_xor_sync(0xffffffffu, v, 4);
             if ((tid & 7) == 0) atomicAdd(d3 + c * HID + m.og + 16 * j, v);
         }
-    if (m.it2 == 0) {
-#pragma unroll
-        for (int j = 0; j < 4; ++j) atomicAdd(a.d_b2 + m.ot2 + 16 * j, g.b2[j]);
+        float v = wg.b2[j];
+        v += __shfl_xor_sync(0xffffffffu, v, 1);
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        if ((tid & 7) == 0) atomicAdd(a.d_b2 + m.og + 16 * j, v);
     }
-    if (m.it1 == 0) {
+    // db1: lanes with the same t hold partial sums over different rows
 #pragma unroll
-        for (int j = 0; j < 4; ++j) atomicAdd(a.d_b1 + m.ot1 + 16 * j, g.b1[j]);
-    }
+    for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+            float v = wg.b1[nt][i];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (m.g == 0) atomicAdd(a.d_b1 + 16 * m.ob + 8 * nt + 2 * m.t + i, v);
+        }
     __syncthreads();
     if (tid < 4) {
         atomicAdd(a.d_b3 + tid, db3s[tid]);
         db3s[tid] = 0.f;
     }
-    wgrad_zero(g);
+    wgrad_zero(wg);
 }
 
-// forward layer: dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2   (same as render.cu)
-template <int K, int WS>
-__device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, const float* bias, float* dst, int cnt,
+// forward layer on the tensor pipe: dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2
+// warp tile: points 32*pb .. +31, outs 16*ob .. +15
+template <int K>
+__device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, int ws, const float* bias, float* dst,
                                               const Maps& m) {
-    if (4 * (m.pq & ~7) >= cnt) return;
-    float acc[4][4];
+    float acc[2][2][4];
+    gemm_pts_mma<K, 2>(src, Wm, ws, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
-    for (int p = 0; p < 4; ++p)
+    for (int nt = 0; nt < 2; ++nt) {
+        const int col = 16 * m.ob + 8 * nt + 2 * m.t;
+        const float b0 = bias[col], b1 = bias[col + 1];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[p][j] = 0.f;
-    gemm_kvec<K, WS>(src, Wm, m.pq, m.og, acc);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        const int o = m.og + 16 * j;
-        const float bo = bias[o];
-        *reinterpret_cast<float4*>(dst + o * AS + 4 * m.pq) =
-            make_float4(lrelu_s2(acc[0][j] + bo), lrelu_s2(acc[1][j] + bo), lrelu_s2(acc[2][j] + bo),
-                        lrelu_s2(acc[3][j] + bo));
+        for (int mt = 0; mt < 2; ++mt) {
+            float* d0 = dst + col * AS + 32 * m.pb + 16 * mt + m.g;
+            d0[0] = lrelu_s2(acc[mt][nt][0] + b0);
+            d0[AS] = lrelu_s2(acc[mt][nt][1] + b1);
+            d0[8] = lrelu_s2(acc[mt][nt][2] + b0);
+            d0[AS + 8] = lrelu_s2(acc[mt][nt][3] + b1);
+        }
     }
 }
 
@@ -239,6 +262,10 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
             if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
             load_part_params(s.part, sc, b, tid, NT);
             load_decoder_smem(s.dec, sc, b, tid);
+            for (int e = tid; e < HID * HID; e += NT)      // w2t[i][o] = W2[o][i]
+                s.w2t[(e % HID) * W2S + e / HID] = sc.w2[(size_t)b * HID * HID + e];
+            for (int e = tid; e < HID * FEAT; e += NT)     // w1t[c][o] = W1[o][c]
+                s.w1t[(e % FEAT) * W2S + e / FEAT] = sc.w1[(size_t)b * HID * FEAT + e];
             cur_b = b;
         }
         if (tid < rays) {
@@ -320,15 +347,15 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
         // ---- 3. per chunk: records -> gather -> decoder forward -> decoder backward -> scatter -------
         for (int c0 = 0; c0 < n_active;) {
             const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
-            const int cend = (cnt + 31) & ~31, nquads = (cnt + 3) >> 2;
+            const int cend = (cnt + 31) & ~31;
             const bool tile_on = 4 * (m.pq & ~7) < cnt;   // this warp's 32 points intersect the chunk
             setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             __syncthreads();
             gather_chunk<T, true>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
             __syncthreads();
-            decoder_layer<FEAT, W1S>(s.X, s.dec.w1, s.dec.b1, s.A1, cnt, m);
+            if (tile_on) decoder_layer<FEAT>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
-            decoder_layer<HID, W2S>(s.A1, s.dec.w2, s.dec.b2, s.A2, cnt, m);
+            if (tile_on) decoder_layer<HID>(s.A1, s.dec.w2, W2S, s.dec.b2, s.A2, m);
             __syncthreads();
             if (8 * warp < cend) {   // head forward + backward: four lanes per point, lane c owns output c
                 const int pt = tid >> 2, c = tid & 3;
@@ -377,40 +404,51 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
                         d.w = fmaf(w, g3[c].w, d.w);
                         wg.w3[c][j] += (g3[c].x * a2.x + g3[c].y * a2.y) + (g3[c].z * a2.z + g3[c].w * a2.w);
                     }
-                    *reinterpret_cast<float4*>(ap) =
-                        make_float4(d.x * act_grad(a2.x), d.y * act_grad(a2.y), d.z * act_grad(a2.z), d.w * act_grad(a2.w));
+                    d = make_float4(d.x * act_grad(a2.x), d.y * act_grad(a2.y), d.z * act_grad(a2.z), d.w * act_grad(a2.w));
+                    *reinterpret_cast<float4*>(ap) = d;
+                    wg.b2[j] += (d.x + d.y) + (d.z + d.w);
                 }
             }
             __syncthreads();
-            wgrad_tile<2, 16>(s.A2, s.A1, m.ot2, m.it2, m.h2, nquads, wg.w2, wg.b2);   // dW2 += G2^T A1, db2
+            // dW2 += G2^T A1 over the chunk's points: warp tile rows (o) 16 pb.., cols (i) 16 ob..
+            wgrad_mma<2>(s.A2, s.A1, 16 * m.pb, 16 * m.ob, cend, m.g, m.t, wg.w2);
             __syncthreads();
-            if (tile_on) {   // G1 = (G2 W2) * act'(a1), in place over A1
-                float acc[4][4];
+            if (tile_on) {   // G1 = (G2 W2) * act'(a1), in place over A1; db1 partial sums
+                float acc[2][2][4];
+                gemm_pts_mma<HID, 2>(s.A2, s.w2t, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
-                for (int p = 0; p < 4; ++p)
+                for (int nt = 0; nt < 2; ++nt) {
+                    const int col = 16 * m.ob + 8 * nt + 2 * m.t;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) acc[p][i] = 0.f;
-                gemm_kmajor<HID, W2S, 4>(s.A2, s.dec.w2, m.pq, 4 * m.og, acc);
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    float* ap = s.A1 + (4 * m.og + i) * AS + 4 * m.pq;
-                    const float4 a1 = *reinterpret_cast<const float4*>(ap);
-                    *reinterpret_cast<float4*>(ap) = make_float4(acc[0][i] * act_grad(a1.x), acc[1][i] * act_grad(a1.y),
-                                                                 acc[2][i] * act_grad(a1.z), acc[3][i] * act_grad(a1.w));
+                    for (int mt = 0; mt < 2; ++mt) {
+                        float* d0 = s.A1 + col * AS + 32 * m.pb + 16 * mt + m.g;
+                        const float g0 = acc[mt][nt][0] * act_grad(d0[0]), g1 = acc[mt][nt][1] * act_grad(d0[AS]);
+                        const float g2 = acc[mt][nt][2] * act_grad(d0[8]), g3 = acc[mt][nt][3] * act_grad(d0[AS + 8]);
+                        d0[0] = g0;
+                        d0[AS] = g1;
+                        d0[8] = g2;
+                        d0[AS + 8] = g3;
+                        wg.b1[nt][0] += g0 + g2;
+                        wg.b1[nt][1] += g1 + g3;
+                    }
                 }
             }
             __syncthreads();
-            wgrad_tile<4, 8>(s.A1, s.X, m.ot1, m.it1, m.h1, nquads, wg.w1, wg.b1);      // dW1 += G1^T X, db1
+            // dW1 += G1^T X: warp tile rows (o) 16 pb.., cols (c) 8 ob..
+            wgrad_mma<1>(s.A1, s.X, 16 * m.pb, 8 * m.ob, cend, m.g, m.t, wg.w1);
             __syncthreads();
-            if (tile_on) {   // dX = G1 W1, in place over X
-                float acc[4][2];
+            if (tile_on) {   // dX = G1 W1, in place over X: warp tile points 32 pb.., channels 8 ob..
+                float acc[2][1][4];
+                gemm_pts_mma<HID, 1>(s.A1, s.w1t, W2S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
+                const int col = 8 * m.ob + 2 * m.t;
 #pragma unroll
-                for (int p = 0; p < 4; ++p) acc[p][0] = acc[p][1] = 0.f;
-                gemm_kmajor<HID, W1S, 2>(s.A1, s.dec.w1, m.pq, 2 * m.og, acc);
-#pragma unroll
-                for (int i = 0; i < 2; ++i)
-                    *reinterpret_cast<float4*>(s.X + (2 * m.og + i) * AS + 4 * m.pq) =
-                        make_float4(acc[0][i], acc[1][i], acc[2][i], acc[3][i]);
+                for (int mt = 0; mt < 2; ++mt) {
+                    float* d0 = s.X + col * AS + 32 * m.pb + 16 * mt + m.g;
+                    d0[0] = acc[mt][0][0];
+                    d0[AS] = acc[mt][0][1];
+                    d0[8] = acc[mt][0][2];
+                    d0[AS + 8] = acc[mt][0][3];
+                }
             }
             __syncthreads();
             scatter_chunk<T>(s.t, s.r.rec, s.X, a, b, c0, c1, tid);

@@ -28,11 +28,11 @@
 #define NWARP (NT / 32)
 #define CH 128             // active points per chunk
 #define AS 132             // activation row stride in floats (rows 16-B aligned, row r starts at bank 4r)
-#define W1S 36             // decoder weight row strides: consecutive rows start 4 banks apart
-#define W2S 68
+#define W1S 40             // decoder weight row strides (8 mod 32: 64-bit mma B-fragment loads are conflict-free)
+#define W2S 72
 #define TP_MAX 1024        // points per tile
 #define MAX_RAYS 32        // rays per tile
-#define PB 512             // (point, part) pair records per chunk
+#define PB 384             // (point, part) pair records per chunk
 #define REC 20             // words per record; 20*r mod 32 hits 8 distinct 4-bank groups for r..r+7
 static_assert(TP_MAX == 2 * NT, "the prefix scan handles two list entries per thread");
 
