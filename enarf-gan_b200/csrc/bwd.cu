@@ -22,6 +22,7 @@ struct BwdArgs {
     enarf_scene_t sc;
     TileGeom g;
     const float* saved;       // (B,n,S,4)
+    const float* feat;        // (B,n,S,32) forward's feature checkpoint | NULL (gather again)
     const float* g_color;     // (B,3,n) | NULL
     const float* g_mask;      // (B,n)   | NULL
     const float* g_disp;      // (B,n)   | NULL
@@ -350,8 +351,22 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
             const int cend = (cnt + 31) & ~31;
             const bool tile_on = 4 * (m.pq & ~7) < cnt;   // this warp's 32 points intersect the chunk
             setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
-            __syncthreads();
-            gather_chunk<T, true>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
+            if (a.feat) {   // features checkpointed by the forward: 8 lanes per point, one 128-B row each
+                const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
+                const int l8 = tid & 7;
+                for (int q = tid >> 3; q < cend; q += NT / 8) {
+                    const float4 f = q < cnt ? __ldg(fi + (size_t)s.t.list[c0 + q] * (FEAT / 4) + l8)
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+                    float* dst = s.X + (l8 * 4) * AS + q;
+                    dst[0] = f.x;
+                    dst[AS] = f.y;
+                    dst[2 * AS] = f.z;
+                    dst[3 * AS] = f.w;
+                }
+            } else {
+                __syncthreads();
+                gather_chunk<T, true>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
+            }
             __syncthreads();
             if (tile_on) decoder_layer<FEAT>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
@@ -460,7 +475,8 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
 }
 
 extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
-                                     const float* ray_dir, const float* bins, const float* point_saved, int n, int Nf,
+                                     const float* ray_dir, const float* bins, const float* point_saved,
+                                     const float* feat_saved, int n, int Nf,
                                      const float* g_color, const float* g_mask, const float* g_disparity,
                                      const float* g_fine_weights, float* d_feat, float* d_prob,
                                      int64_t d_prob_batch_stride, float* d_w1, float* d_w2, float* d_w3, float* d_b1,
@@ -471,8 +487,8 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
                   "enarf_render_fine_bwd: NULL forward argument");
     ENARF_REQUIRE(d_feat && d_prob && d_w1 && d_w2 && d_w3 && d_b1 && d_b2 && d_b3, ENARF_ERR_INVALID_ARG,
                   "enarf_render_fine_bwd: NULL gradient buffer");
-    ENARF_REQUIRE(((uintptr_t)d_feat & 15) == 0 && ((uintptr_t)point_saved & 15) == 0, ENARF_ERR_INVALID_ARG,
-                  "enarf_render_fine_bwd: d_feat / point_saved must be 16-byte aligned");
+    ENARF_REQUIRE(((uintptr_t)d_feat & 15) == 0 && ((uintptr_t)point_saved & 15) == 0 && ((uintptr_t)feat_saved & 15) == 0,
+                  ENARF_ERR_INVALID_ARG, "enarf_render_fine_bwd: d_feat / point_saved / feat_saved must be 16-byte aligned");
     ENARF_REQUIRE(n > 0 && Nf >= 2, ENARF_ERR_INVALID_ARG, "enarf_render_fine_bwd: bad sizes n=%d Nf=%d", n, Nf);
     ENARF_REQUIRE(Nf <= TP_MAX, ENARF_ERR_UNSUPPORTED, "enarf_render_fine_bwd: Nf=%d exceeds %d", Nf, TP_MAX);
     BwdArgs a = {};
@@ -485,6 +501,7 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     a.g.S = Nf;
     a.g.skip_last = 1;
     a.saved = point_saved;
+    a.feat = feat_saved;
     a.g_color = g_color;
     a.g_mask = g_mask;
     a.g_disp = g_disparity;

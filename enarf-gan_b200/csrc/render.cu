@@ -32,6 +32,7 @@ struct RenderArgs {
     float* disp;
     float* fine_weights;
     float* point_out;
+    float* feat_out;    // (B,n,S,32) checkpoint of the gathered features for the backward, or NULL
     float* q_density;
     float* q_color;
     uint32_t* q_mask;
@@ -97,6 +98,12 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
                 if (a0 >= n_active) break;
                 const int np = min(32, n_active - a0);
                 gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane);
+                if (MODE == MODE_FINE && a.feat_out) {   // 8 lanes per point: one 128-B row each
+                    float4* fo = reinterpret_cast<float4*>(a.feat_out) + ((size_t)b * n + ray0) * S * (FEAT / 4);
+                    for (int q = lane >> 3; q < np; q += 4)
+                        fo[(size_t)s.t.list[a0 + q] * (FEAT / 4) + (lane & 7)] =
+                            *reinterpret_cast<const float4*>(my.X + q * XSW + 4 * (lane & 7));
+                }
                 float o3[2][4];
                 decode32_mma(my.X, s.dec, lane, o3);
                 __syncwarp();   // every lane is done reading X before the next chunk's gather overwrites it
@@ -259,15 +266,15 @@ extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* dept
 extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                      const float* ray_dir, const float* bins, int n, int Nf, float* color,
                                      float* mask, float* disparity, float* fine_weights, float* fine_depth,
-                                     float* point_out, void* stream) {
+                                     float* point_out, float* feat_out, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_fwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && color && mask && disparity && fine_weights && fine_depth,
                   ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: NULL argument");
     ENARF_REQUIRE(n > 0 && Nf >= 2, ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: bad sizes n=%d Nf=%d", n, Nf);
     ENARF_REQUIRE(Nf <= TP_MAX, ENARF_ERR_UNSUPPORTED, "enarf_render_fine_fwd: Nf=%d exceeds %d", Nf, TP_MAX);
-    ENARF_REQUIRE(!point_out || ((uintptr_t)point_out & 15) == 0, ENARF_ERR_INVALID_ARG,
-                  "enarf_render_fine_fwd: point_out must be 16-byte aligned");
+    ENARF_REQUIRE((!point_out || ((uintptr_t)point_out & 15) == 0) && (!feat_out || ((uintptr_t)feat_out & 15) == 0),
+                  ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: point_out / feat_out must be 16-byte aligned");
     RenderArgs a = {};
     a.sc = *scene;
     a.g.dmin = depth_min;
@@ -284,6 +291,7 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
     a.disp = disparity;
     a.fine_weights = fine_weights;
     a.point_out = point_out;
+    a.feat_out = feat_out;
     return launch_render<MODE_FINE>(a, "enarf_render_fine_fwd", (cudaStream_t)stream);
 }
 

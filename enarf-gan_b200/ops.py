@@ -10,6 +10,9 @@ from ._abi import check, lib, ptr, stream_ptr
 
 FEAT_DIM = 32
 HIDDEN = 64
+# Checkpoint the gathered features (B,n,Nf,32) in the forward so the backward skips its gather; costs 128 B per
+# fine sample of device memory.  Set False to recompute instead.
+SAVE_FEATURES = True
 
 
 class SceneBuffers:
@@ -133,7 +136,9 @@ def density_query(scene, points, want_color=True, want_mask=False):
     return den, col, msk
 
 
-def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False):
+def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False):
+    """-> color, mask, disp, fine_weights, fine_depth [, points (B,n,Nf,4)] [, feat (B,n,Nf,32) checkpoint: only
+    the rows of samples inside a part are written]."""
     B, n, Nf = bins.shape
     dev = bins.device
     color = torch.empty(B, 3, n, device=dev)
@@ -142,9 +147,16 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False):
     fw = torch.empty(B, n, Nf - 1, device=dev)
     fd = torch.empty(B, n, Nf, device=dev)
     pts = torch.empty(B, n, Nf, 4, device=dev) if want_points else None
+    feat = torch.empty(B, n, Nf, FEAT_DIM, device=dev) if want_feat else None
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
-                                      ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True), stream_ptr()))
-    return (color, mask, disp, fw, fd, pts) if want_points else (color, mask, disp, fw, fd)
+                                      ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True),
+                                      ptr(feat, allow_none=True), stream_ptr()))
+    out = (color, mask, disp, fw, fd)
+    if want_points:
+        out += (pts,)
+    if want_feat:
+        out += (feat,)
+    return out
 
 
 class RenderFine(torch.autograd.Function):
@@ -154,9 +166,10 @@ class RenderFine(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True)
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES)
         ctx.scene = scene
-        ctx.save_for_backward(dmin, dmax, direction, bins, out[5])
+        ctx.save_for_backward(dmin, dmax, direction, bins, out[5], *(out[6:]))
+        out = out[:6]
         ctx.tp_shape = tri_plane.shape
         ctx.mark_non_differentiable(out[4], out[5])
         return out
@@ -164,7 +177,8 @@ class RenderFine(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
         scene = ctx.scene
-        dmin, dmax, direction, bins, pts = ctx.saved_tensors
+        dmin, dmax, direction, bins, pts, *feat = ctx.saved_tensors
+        feat = feat[0] if feat else None
         B, n, Nf = bins.shape
         dev = bins.device
         c = lambda g: None if g is None else g.contiguous().float()
@@ -176,7 +190,7 @@ class RenderFine(torch.autograd.Function):
         db = [torch.zeros_like(b) for b in scene.b]
         g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
         check(lib().enarf_render_fine_bwd(
-            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), n, Nf,
+            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True), n, Nf,
             ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
             ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
             ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))

@@ -100,21 +100,25 @@ int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, con
 /* Fine pass forward, fused gather -> decoder -> compositing (rendering.py:198-200,283-335).
  * bins (B,n,Nf) sorted.  Outputs: color (B,3,n), mask (B,n), disparity (B,n),
  * fine_weights (B,n,Nf-1), fine_depth (B,n,Nf); point_out (B,n,Nf,4) = per-sample (r,g,b,sigma), optional
- * (NULL to skip) -- it is what the backward consumes and what rendering.py:287 exposes as fine_density. */
+ * (NULL to skip) -- it is what the backward consumes and what rendering.py:287 exposes as fine_density;
+ * feat_out (B,n,Nf,32), optional (NULL to skip, the inference path): the gathered, part-weighted feature of
+ * every sample that lies inside at least one part (other rows are left untouched) -- a checkpoint that lets the
+ * backward skip its own gather; 16-byte aligned. */
 int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, int n, int Nf, float* color, float* mask,
                           float* disparity, float* fine_weights, float* fine_depth, float* point_out,
-                          void* stream);
+                          float* feat_out, void* stream);
 
-/* Fine pass backward.  point_saved (B,n,Nf,4) is the forward's point_out.  Upstream gradients (any may be NULL = zero): g_color (B,3,n), g_mask (B,n),
- * g_disparity (B,n), g_fine_weights (B,n,Nf-1).  Gradient buffers (caller zero-initialises; results are
- * ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as scene->prob_planes,
- * d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4). */
+/* Fine pass backward.  point_saved (B,n,Nf,4) is the forward's point_out; feat_saved (B,n,Nf,32) is the forward's
+ * feat_out or NULL (the features are then gathered again).  Upstream gradients (any may be NULL = zero):
+ * g_color (B,3,n), g_mask (B,n), g_disparity (B,n), g_fine_weights (B,n,Nf-1).  Gradient buffers (caller
+ * zero-initialises; results are ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as
+ * scene->prob_planes, d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4). */
 int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
-                          const float* ray_dir, const float* bins, const float* point_saved, int n, int Nf,
-                          const float* g_color, const float* g_mask, const float* g_disparity, const float* g_fine_weights,
-                          float* d_feat, float* d_prob, int64_t d_prob_batch_stride, float* d_w1, float* d_w2,
-                          float* d_w3, float* d_b1, float* d_b2, float* d_b3, void* stream);
+                          const float* ray_dir, const float* bins, const float* point_saved, const float* feat_saved,
+                          int n, int Nf, const float* g_color, const float* g_mask, const float* g_disparity,
+                          const float* g_fine_weights, float* d_feat, float* d_prob, int64_t d_prob_batch_stride,
+                          float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, void* stream);
 
 /* Point query = calc_density_and_color_from_camera_coord_v2 (models/narf.py:176-211): points (B,3,N) in
  * the scaled camera frame -> density (B,1,N), color (B,3,N) (NULL to skip), part_mask (B,N) uint32 bit p =

@@ -67,9 +67,12 @@ def test_fine_pass_gradients(name, dtype, tol, btol):
         assert rel(b.grad, br.grad) < btol, f"db{i + 1}"
 
 
-def test_backward_with_missing_upstream_grads():
-    """Only colour feeds the loss: the NULL-gradient paths of the ABI."""
+@pytest.mark.parametrize("save_features", [True, False])
+def test_backward_with_missing_upstream_grads(save_features, monkeypatch):
+    """Only colour feeds the loss: the NULL-gradient paths of the ABI; with the forward's feature checkpoint
+    (feat_saved) and without it (the backward gathers again)."""
     from enarf_gan_b200 import ops
+    monkeypatch.setattr(ops, "SAVE_FEATURES", save_features)
     g, cfg, inp, tp, layers, z_rend = G.load("b2_s24")
     sc = G.scene(cfg, inp, tp, layers, z_rend, torch.float32)
     B, Nc, Nf = cfg["B"], cfg["Nc"], cfg["Nf"]
