@@ -4,7 +4,10 @@
 // Reference being replaced: autograd through libraries/NeRF/rendering.py:307-335, models/narf.py:213-275,
 // libraries/triplane/sampling.py:54-127 (grid_sample backward + scatter_add backward), NeRF/activation.py:12-16.
 //
-// Same tile framework as the forward (tile.cuh): one 512-thread CTA owns whole rays.  Per tile
+// Same tile framework as the forward (tile.cuh), but with two independent 256-thread CTAs per SM working on
+// 64-point chunks: the phases of a chunk are separated by CTA-wide barriers and alternate between latency-bound
+// (checkpoint load, pair setup, scatter) and tensor-pipe-bound (the GEMMs) work, so a second resident CTA fills
+// the issue slots the first one leaves idle.  Shared memory is kept under 113 KB per CTA for that.  Per tile
 //   1. positions + part masks are regenerated with the forward's contract arithmetic (bit-identical masks);
 //   2. one warp per ray turns the upstream gradients and the forward's saved (rgb, sigma) into per-sample
 //      d/d rgb and d/d sigma (two shuffle scans: transmittance prefix, weighted-gradient suffix), in place;
@@ -15,8 +18,19 @@
 //   4. d(feature) is scattered with 128-bit vector reductions (red.global.add.v4.f32) into the channels-last
 //      gradient planes using the same pair records; d(part weight) goes through the sigmoid product into
 //      scalar reductions on the probability planes.
+#define NT 256
+#define CH 64
+#define AS 68
+#define MAX_RAYS 16
+#define PB 160
 #include "tile.cuh"
 #include "mma_smem.cuh"
+
+#define PBLK (CH / 32)        // 32-point blocks per chunk
+#define WCOL (NWARP / 4)      // column groups of the weight-gradient tiles (4 row blocks of 16 outs each)
+#define TN2 (8 / WCOL)        // 8-column mma tiles per warp: dW2 (64 columns) / dW1 (32 columns)
+#define TN1 (4 / WCOL)
+static_assert(NWARP / PBLK == 4, "a warp's mma tile is 32 points x 16 outs");
 
 struct BwdArgs {
     enarf_scene_t sc;
@@ -37,8 +51,6 @@ struct BwdArgs {
 
 struct __align__(16) BwdSmem {
     DecoderSmem dec;
-    float w2t[HID * W2S];    // [i][o]  W2 transposed: B fragments of G1 = G2 W2
-    float w1t[FEAT * W2S];   // [c][o]  W1 transposed: B fragments of dX = G1 W1
     float part[ENARF_MAX_PARTS * PART_STRIDE];
     TileSmem t;
     RecSmem r;
@@ -61,11 +73,11 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 
 // per-thread weight-gradient accumulators, alive across tiles
 struct WGrad {
-    float w2[1][2][4];   // mma tiles: rows (o) 16*(warp&3)+g(+8), cols (i) 16*(warp>>2) + 8 nt + 2t(+1)
-    float w1[1][1][4];   // rows (o) 16*(warp&3)+g(+8), cols (c) 8*(warp>>2) + 2t(+1)
+    float w2[1][TN2][4]; // mma tiles: rows (o) 16*(warp&3)+g(+8), cols (i) 8*TN2*(warp>>2) + 8 nt + 2t(+1)
+    float w1[1][TN1][4]; // rows (o) 16*(warp&3)+g(+8), cols (c) 8*TN1*(warp>>2) + 8 nt + 2t(+1)
     float w3[4][4];      // [c][j]: row c, col og + 16 j, summed over this thread's point quad
     float b2[4];         // cols og + 16 j, this thread's point quad
-    float b1[2][2];      // cols 16*(warp>>2) + 8 nt + 2t + {0,1}, this lane's rows
+    float b1[2][2];      // cols 16*ob + 8 nt + 2t + {0,1}, this lane's rows
 };
 
 __device__ __forceinline__ void wgrad_zero(WGrad& g) {
@@ -73,26 +85,33 @@ __device__ __forceinline__ void wgrad_zero(WGrad& g) {
     for (int i = 0; i < 4; ++i) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) g.w3[i][j] = 0.f;
-        g.w2[0][0][i] = g.w2[0][1][i] = g.w1[0][0][i] = 0.f;
+#pragma unroll
+        for (int j = 0; j < TN2; ++j) g.w2[0][j][i] = 0.f;
+#pragma unroll
+        for (int j = 0; j < TN1; ++j) g.w1[0][j][i] = 0.f;
         g.b2[i] = 0.f;
     }
     g.b1[0][0] = g.b1[0][1] = g.b1[1][0] = g.b1[1][1] = 0.f;
 }
 
 // thread -> tile coordinates: (pq, og) for the element-wise FP32 passes (4 points x outs og+16j),
-// (pb, ob, g, t) for the mma phases (warp tile: 32 points x 16 outs, or one/two weight-gradient tiles)
+// (pb, ob, g, t) for the point-major mma phases (warp tile: 32 points x 16 outs), (wr, wc) for the
+// weight-gradient tiles (rows 16 wr.., column group wc)
 struct Maps {
     int pq, og;
     int pb, ob, g, t;
+    int wr, wc;
 };
 
 __device__ __forceinline__ Maps make_maps(int tid) {
     const int w = tid >> 5, lane = tid & 31;
     Maps m;
-    m.pq = (w & 3) * 8 + (lane & 7);
-    m.og = (w >> 2) * 4 + (lane >> 3);
-    m.pb = w & 3;
-    m.ob = w >> 2;
+    m.pb = w % PBLK;
+    m.ob = w / PBLK;
+    m.pq = m.pb * 8 + (lane & 7);
+    m.og = m.ob * 4 + (lane >> 3);
+    m.wr = w & 3;
+    m.wc = w >> 2;
     m.g = lane >> 2;
     m.t = lane & 3;
     return m;
@@ -102,21 +121,22 @@ __device__ __forceinline__ void wgrad_flush(WGrad& wg, const Maps& m, float* db3
     float* d1 = a.d_w1 + (size_t)b * HID * FEAT;
     float* d2 = a.d_w2 + (size_t)b * HID * HID;
     float* d3 = a.d_w3 + (size_t)b * 4 * HID;
-    const int r0 = 16 * m.pb + m.g;
+    const int r0 = 16 * m.wr + m.g;
 #pragma unroll
-    for (int nt = 0; nt < 2; ++nt) {
-        const int c = 16 * m.ob + 8 * nt + 2 * m.t;
+    for (int nt = 0; nt < TN2; ++nt) {
+        const int c = 8 * TN2 * m.wc + 8 * nt + 2 * m.t;
         atomicAdd(d2 + r0 * HID + c, wg.w2[0][nt][0]);
         atomicAdd(d2 + r0 * HID + c + 1, wg.w2[0][nt][1]);
         atomicAdd(d2 + (r0 + 8) * HID + c, wg.w2[0][nt][2]);
         atomicAdd(d2 + (r0 + 8) * HID + c + 1, wg.w2[0][nt][3]);
     }
-    {
-        const int c = 8 * m.ob + 2 * m.t;
-        atomicAdd(d1 + r0 * FEAT + c, wg.w1[0][0][0]);
-        atomicAdd(d1 + r0 * FEAT + c + 1, wg.w1[0][0][1]);
-        atomicAdd(d1 + (r0 + 8) * FEAT + c, wg.w1[0][0][2]);
-        atomicAdd(d1 + (r0 + 8) * FEAT + c + 1, wg.w1[0][0][3]);
+#pragma unroll
+    for (int nt = 0; nt < TN1; ++nt) {
+        const int c = 8 * TN1 * m.wc + 8 * nt + 2 * m.t;
+        atomicAdd(d1 + r0 * FEAT + c, wg.w1[0][nt][0]);
+        atomicAdd(d1 + r0 * FEAT + c + 1, wg.w1[0][nt][1]);
+        atomicAdd(d1 + (r0 + 8) * FEAT + c, wg.w1[0][nt][2]);
+        atomicAdd(d1 + (r0 + 8) * FEAT + c + 1, wg.w1[0][nt][3]);
     }
     // dW3 / db2: the 8 lanes that share an out group hold partial sums over different point quads
 #pragma unroll
@@ -160,7 +180,7 @@ template <int K>
 __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, int ws, const float* bias, float* dst,
                                               const Maps& m) {
     float acc[2][2][4];
-    gemm_pts_mma<K, 2>(src, Wm, ws, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
+    gemm_pts_mma<K, 2, false>(src, Wm, ws, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
         const int col = 16 * m.ob + 8 * nt + 2 * m.t;
@@ -236,7 +256,7 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
 }
 
 template <typename T>
-__global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
+__global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BwdSmem& s = *reinterpret_cast<BwdSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -263,10 +283,6 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
             if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
             load_part_params(s.part, sc, b, tid, NT);
             load_decoder_smem(s.dec, sc, b, tid);
-            for (int e = tid; e < HID * HID; e += NT)      // w2t[i][o] = W2[o][i]
-                s.w2t[(e % HID) * W2S + e / HID] = sc.w2[(size_t)b * HID * HID + e];
-            for (int e = tid; e < HID * FEAT; e += NT)     // w1t[c][o] = W1[o][c]
-                s.w1t[(e % FEAT) * W2S + e / FEAT] = sc.w1[(size_t)b * HID * FEAT + e];
             cur_b = b;
         }
         if (tid < rays) {
@@ -349,7 +365,7 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
         for (int c0 = 0; c0 < n_active;) {
             const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
             const int cend = (cnt + 31) & ~31;
-            const bool tile_on = 4 * (m.pq & ~7) < cnt;   // this warp's 32 points intersect the chunk
+            const bool tile_on = 32 * m.pb < cnt;   // this warp's 32 points intersect the chunk
             setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             if (a.feat) {   // features checkpointed by the forward: 8 lanes per point, one 128-B row each
                 const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
@@ -425,12 +441,12 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
-            // dW2 += G2^T A1 over the chunk's points: warp tile rows (o) 16 pb.., cols (i) 16 ob..
-            wgrad_mma<2>(s.A2, s.A1, 16 * m.pb, 16 * m.ob, cend, m.g, m.t, wg.w2);
+            // dW2 += G2^T A1 over the chunk's points: warp tile rows (o) 16 wr.., cols (i) 8 TN2 wc..
+            wgrad_mma<TN2>(s.A2, s.A1, 16 * m.wr, 8 * TN2 * m.wc, cend, m.g, m.t, wg.w2);
             __syncthreads();
             if (tile_on) {   // G1 = (G2 W2) * act'(a1), in place over A1; db1 partial sums
                 float acc[2][2][4];
-                gemm_pts_mma<HID, 2>(s.A2, s.w2t, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
+                gemm_pts_mma<HID, 2, true>(s.A2, s.dec.w2, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
                 for (int nt = 0; nt < 2; ++nt) {
                     const int col = 16 * m.ob + 8 * nt + 2 * m.t;
@@ -449,12 +465,12 @@ __global__ void __launch_bounds__(NT, 1) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
-            // dW1 += G1^T X: warp tile rows (o) 16 pb.., cols (c) 8 ob..
-            wgrad_mma<1>(s.A1, s.X, 16 * m.pb, 8 * m.ob, cend, m.g, m.t, wg.w1);
+            // dW1 += G1^T X: warp tile rows (o) 16 wr.., cols (c) 8 TN1 wc..
+            wgrad_mma<TN1>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
             __syncthreads();
             if (tile_on) {   // dX = G1 W1, in place over X: warp tile points 32 pb.., channels 8 ob..
                 float acc[2][1][4];
-                gemm_pts_mma<HID, 1>(s.A1, s.w1t, W2S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
+                gemm_pts_mma<HID, 1, true>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
                 const int col = 8 * m.ob + 2 * m.t;
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {
@@ -518,8 +534,9 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     a.rays_per_tile = max(1, min(MAX_RAYS, TP_MAX / Nf));
     a.tiles_per_sample = (n + a.rays_per_tile - 1) / a.rays_per_tile;
     const int total = scene->B * a.tiles_per_sample;
-    const int grid = min(total, enarf_sm_count());
+    const int grid = min(total, 2 * enarf_sm_count());
     const size_t smem = sizeof(BwdSmem);
+    static_assert(sizeof(BwdSmem) <= 113 * 1024, "two CTAs per SM");
     a.tile_counter = enarf_tile_counter((cudaStream_t)stream);
     if (!a.tile_counter) return ENARF_ERR_CUDA;
     cudaError_t e;

@@ -27,6 +27,13 @@ __device__ __forceinline__ void fragB_w(const float* __restrict__ Wm, int ws, in
     split_tf32(v.x, f.h0, f.l0);
     split_tf32(v.y, f.h1, f.l1);
 }
+// cols = n0+g, k = rows k0+2t, k0+2t+1 of a matrix stored W[k][n] (row stride ws = 8 mod 32: banks 16t+g, a 2-way
+// conflict accepted to avoid a transposed copy of the weights in shared memory)
+__device__ __forceinline__ void fragB_kn(const float* __restrict__ Wm, int ws, int k0, int n0, int g, int t, FragB& f) {
+    const float* p = Wm + (k0 + 2 * t) * ws + n0 + g;
+    split_tf32(p[0], f.h0, f.l0);
+    split_tf32(p[ws], f.h1, f.l1);
+}
 // weight gradients: rows = channels m0+g (+8) of M[channel][point], k = points k0+t, k0+t+4
 __device__ __forceinline__ void fragA_rowk(const float* __restrict__ M, int m0, int k0, int g, int t, FragA& f) {
     const float* p = M + (m0 + g) * AS + k0 + t;
@@ -60,8 +67,9 @@ __device__ __forceinline__ void mma3_tiles(float (&acc)[TM][TN][4], const FragA 
         for (int nt = 0; nt < TN; ++nt) mma_tf32(acc[mt][nt], a[mt].h, b[nt].h0, b[nt].h1);
 }
 
-// out[pt][n] = sum_k Act[k][pt] * Wm[n][k] for this warp's 32 points (m0, m0+16) and TN n-tiles from n0
-template <int K, int TN>
+// out[pt][n] = sum_k Act[k][pt] * W(n,k) for this warp's 32 points (m0, m0+16) and TN n-tiles from n0;
+// W(n,k) = Wm[n][k] (KN = false) or Wm[k][n] (KN = true)
+template <int K, int TN, bool KN>
 __device__ __forceinline__ void gemm_pts_mma(const float* __restrict__ Act, const float* __restrict__ Wm, int ws, int m0,
                                              int n0, int g, int t, float (&acc)[2][TN][4]) {
 #pragma unroll
@@ -77,7 +85,10 @@ __device__ __forceinline__ void gemm_pts_mma(const float* __restrict__ Act, cons
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) fragA_chpt(Act, k0, m0 + 16 * mt, g, t, a[mt]);
 #pragma unroll
-        for (int nt = 0; nt < TN; ++nt) fragB_w(Wm, ws, k0, n0 + 8 * nt, g, t, b[nt]);
+        for (int nt = 0; nt < TN; ++nt) {
+            if (KN) fragB_kn(Wm, ws, k0, n0 + 8 * nt, g, t, b[nt]);
+            else fragB_w(Wm, ws, k0, n0 + 8 * nt, g, t, b[nt]);
+        }
         mma3_tiles<2, TN>(acc, a, b);
     }
 }

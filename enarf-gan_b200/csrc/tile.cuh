@@ -24,15 +24,27 @@
 #include "common.cuh"
 #include "gather.cuh"
 
+// Geometry of the CTA; a translation unit may pre-define these before including this header (bwd.cu runs two
+// 256-thread CTAs per SM on 64-point chunks, render.cu one 512-thread CTA per SM).
+#ifndef NT
 #define NT 512             // threads per CTA
+#endif
 #define NWARP (NT / 32)
+#ifndef CH
 #define CH 128             // active points per chunk
-#define AS 132             // activation row stride in floats (rows 16-B aligned, row r starts at bank 4r)
+#endif
+#ifndef AS
+#define AS 132             // activation row stride in floats (rows 16-B aligned; AS % 32 == 4: row r starts at bank 4r)
+#endif
 #define W1S 40             // decoder weight row strides (8 mod 32: 64-bit mma B-fragment loads are conflict-free)
 #define W2S 72
-#define TP_MAX 1024        // points per tile
+#define TP_MAX (2 * NT)    // points per tile
+#ifndef MAX_RAYS
 #define MAX_RAYS 32        // rays per tile
+#endif
+#ifndef PB
 #define PB 384             // (point, part) pair records per chunk
+#endif
 #define REC 20             // words per record; 20*r mod 32 hits 8 distinct 4-bank groups for r..r+7
 static_assert(TP_MAX == 2 * NT, "the prefix scan handles two list entries per thread");
 
