@@ -18,7 +18,11 @@
 #include "common.cuh"
 #include "gather.cuh"
 
-#define XS 40    // row stride (floats) of the per-warp feature slab X[point][channel]: 8g + 2t covers 32 banks
+// Per-warp feature slab X[point][channel]: dense 32-float rows, the four 8-float granules of row r stored at
+// granule index j ^ (r & 3).  A-fragment loads (64-bit, rows g / g+8, column 8j+2t) then hit bank
+// 8*(j ^ (g&3)) + 2t: conflict-free per half-warp, with no padding.
+#define XS 32
+__device__ __forceinline__ int xs_col(int row, int col) { return col ^ (8 * (row & 3)); }
 #define W1M 40   // weight row strides for the 64-bit B-fragment loads (same bank argument)
 #define W2M 72
 
@@ -83,8 +87,9 @@ __device__ __forceinline__ void decode32_mma(const float* __restrict__ X, const 
         uint32_t ah[2][4], al[2][4];
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
-            const float2 v0 = *reinterpret_cast<const float2*>(X + (16 * mt + g) * XS + 8 * j + 2 * t);
-            const float2 v1 = *reinterpret_cast<const float2*>(X + (16 * mt + g + 8) * XS + 8 * j + 2 * t);
+            const int col = xs_col(g, 8 * j + 2 * t);   // rows g, g+8, g+16, g+24 share (row & 3)
+            const float2 v0 = *reinterpret_cast<const float2*>(X + (16 * mt + g) * XS + col);
+            const float2 v1 = *reinterpret_cast<const float2*>(X + (16 * mt + g + 8) * XS + col);
             split_tf32(v0.x, ah[mt][0], al[mt][0]);
             split_tf32(v1.x, ah[mt][1], al[mt][1]);
             split_tf32(v0.y, ah[mt][2], al[mt][2]);

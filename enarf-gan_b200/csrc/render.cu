@@ -14,6 +14,9 @@
 // Per-point features, activations, densities and colours live only in shared memory / registers.  The grid is
 // persistent and pulls tiles in sample-major order from an atomic counter so that one sample's planes stay
 // L2-resident and the decoder weights are reloaded only when the sample changes.
+#define NT 256
+#define MAX_RAYS 16
+#define RECW 52
 #include "tile.cuh"
 #include "mlp_mma.cuh"
 
@@ -46,8 +49,8 @@ struct __align__(16) WarpSlab {
 struct __align__(16) FwdSmem {
     DecoderMma dec;
     float part[ENARF_MAX_PARTS * PART_STRIDE];
-    TileSmem t;
-    float4 out[TP_MAX];       // r, g, b, sigma per point (coarse: .x is reused for the alpha weight)
+    TileSmem t;               // t.pm[i] = (x, y, z, part mask) is overwritten by (r, g, b, sigma) once point i is
+                              // decoded; a point outside every part keeps mask bits 0 == sigma 0.0f
     union {
         WarpSlab slab[NWARP];
         float cull[MAX_RAYS * ENARF_MAX_PARTS * 2];   // phase 0/1 only (tile_points sees it as RecSmem::cull)
@@ -56,7 +59,7 @@ struct __align__(16) FwdSmem {
 static_assert(XSW == XS, "gather slab stride must match the decoder's A-fragment loads");
 
 template <int MODE, typename T>
-__global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
+__global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FwdSmem& s = *reinterpret_cast<FwdSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -80,11 +83,12 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
             load_decoder_mma(s.dec, sc, b, tid, NT);
             cur_b = b;
         }
-        for (int i = tid; i < tp; i += NT) s.out[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (tid == 0) s.t.pad_[0] = 0;   // chunk counter of this tile
-        __syncthreads();
         tile_points<MODE>(s.t, *reinterpret_cast<RecSmem*>(&s.u), s.part, a.g, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
+        if (MODE == MODE_QUERY && a.q_mask)
+            for (int i = tid; i < tp; i += NT) a.q_mask[(size_t)b * n + ray0 + i] = __float_as_uint(s.t.pm[i].w);
+        float4* out = s.t.pm;
 
         // ---- chunks of 32 active points, one warp each, no CTA barrier ---------------------------------
         {
@@ -102,7 +106,7 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
                     float4* fo = reinterpret_cast<float4*>(a.feat_out) + ((size_t)b * n + ray0) * S * (FEAT / 4);
                     for (int q = lane >> 3; q < np; q += 4)
                         fo[(size_t)s.t.list[a0 + q] * (FEAT / 4) + (lane & 7)] =
-                            *reinterpret_cast<const float4*>(my.X + q * XSW + 4 * (lane & 7));
+                            *reinterpret_cast<const float4*>(my.X + q * XSW + xs_col(q, 4 * (lane & 7)));
                 }
                 float o3[2][4];
                 decode32_mma(my.X, s.dec, lane, o3);
@@ -120,7 +124,7 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
                                 const float v0 = lrelu_s2(o3[mt][2 * h]), v1 = lrelu_s2(o3[mt][2 * h + 1]);
                                 const float2 r = t4 == 0 ? make_float2(tanhf(v0), tanhf(v1))
                                                          : make_float2(tanhf(v0), fmaxf(v1, 0.f) * 10.f);
-                                reinterpret_cast<float2*>(&s.out[s.t.list[a0 + row]])[t4] = r;
+                                reinterpret_cast<float2*>(&out[s.t.list[a0 + row]])[t4] = r;
                             }
                         }
                 }
@@ -131,7 +135,8 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
         // ---- outputs ---------------------------------------------------------------------------------
         if (MODE == MODE_QUERY) {
             for (int i = tid; i < tp; i += NT) {
-                const float4 o = s.out[i];
+                const bool on = (s.t.act[i >> 5] >> (i & 31)) & 1;
+                const float4 o = on ? out[i] : make_float4(0.f, 0.f, 0.f, 0.f);
                 const size_t gi = (size_t)b * n + ray0 + i;
                 if (a.q_density) a.q_density[gi] = o.w;
                 if (a.q_color) {
@@ -140,16 +145,16 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
                     c[n] = o.y;
                     c[2 * (size_t)n] = o.z;
                 }
-                if (a.q_mask) a.q_mask[gi] = __float_as_uint(s.t.pm[i].w);
             }
             continue;
         }
         if (MODE == MODE_FINE && a.point_out) {
             float4* dst = reinterpret_cast<float4*>(a.point_out) + ((size_t)b * n + ray0) * S;
-            for (int i = tid; i < tp; i += NT) dst[i] = s.out[i];
+            for (int i = tid; i < tp; i += NT)
+                dst[i] = ((s.t.act[i >> 5] >> (i & 31)) & 1) ? out[i] : make_float4(0.f, 0.f, 0.f, 0.f);
         }
         const int M = (MODE == MODE_COARSE) ? S : S - 1;  // intervals that carry weight
-        float* outf = reinterpret_cast<float*>(s.out);
+        float* outf = reinterpret_cast<float*>(out);   // rgb of points outside every part is never weighted (sigma 0)
         for (int r = warp; r < rays; r += NWARP) {
             const float* dep = s.t.depth + r * (S + 1);
             float* po = outf + (size_t)r * S * 4;
@@ -216,8 +221,9 @@ __global__ void __launch_bounds__(NT, 1) render_kernel(const RenderArgs a) {
 template <int MODE>
 static int launch_render(RenderArgs& a, const char* who, cudaStream_t stream) {
     const int total = a.sc.B * a.tiles_per_sample;
-    const int grid = min(total, enarf_sm_count());
+    const int grid = min(total, 2 * enarf_sm_count());
     const size_t smem = sizeof(FwdSmem);
+    static_assert(sizeof(FwdSmem) <= 113 * 1024, "two CTAs per SM");
     a.tile_counter = enarf_tile_counter(stream);
     if (!a.tile_counter) return ENARF_ERR_CUDA;
     cudaError_t e;

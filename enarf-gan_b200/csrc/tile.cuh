@@ -67,6 +67,7 @@ struct __align__(16) TileSmem {
     uint32_t cand[MAX_RAYS];
     uint16_t list[TP_MAX];
     uint16_t pref[TP_MAX + 8];
+    uint32_t act[TP_MAX / 32];         // bit i%32 of word i/32: point i is inside at least one part
     int wsum[NWARP];
     int n_active;
     int tile;
@@ -189,6 +190,7 @@ __device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float
             t.pm[i] = make_float4(x, y, z, __uint_as_float(m));
         }
         const uint32_t bal = __ballot_sync(0xffffffffu, m != 0);
+        if (lane == 0) t.act[i >> 5] = bal;
         if (bal) {
             int base = 0;
             if (lane == 0) base = atomicAdd(&t.n_active, __popc(bal));
@@ -482,8 +484,10 @@ __device__ __forceinline__ void gemm_kvec2(const float* __restrict__ act, const 
 
 // ---- warp-autonomous gather (forward): one warp owns the 32 active points [a, a+np) of a chunk ----------
 // Records go to the warp's own slab `rec` (RECW records), features to its slab X[point][XSW]; only __syncwarp.
+#ifndef RECW
 #define RECW 48     // pair records per warp sub-batch (one point has at most 32 pairs)
-#define XSW 40      // feature slab row stride (see mlp_mma.cuh XS)
+#endif
+#define XSW 32      // feature slab row stride; 8-float granules are XOR-swizzled by the row (mlp_mma.cuh xs_col)
 
 template <typename T>
 __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, float* X, const float* s_part,
@@ -553,7 +557,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
                     }
                 }
             }
-            *reinterpret_cast<float4*>(X + q * XSW + 4 * lane8) = f;
+            *reinterpret_cast<float4*>(X + q * XSW + ((4 * lane8) ^ (8 * (q & 3)))) = f;
         }
         __syncwarp();
         q0 = q1;
