@@ -222,12 +222,10 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
             const float4 w4 = rp[1 + k];
             w[4 * k] = w4.x; w[4 * k + 1] = w4.y; w[4 * k + 2] = w4.z; w[4 * k + 3] = w4.w;
         }
-        // all texel loads first (independent), then the dot products and the reductions
+        // all texel loads first (independent, always in range), then the dot products and the reductions
         float4 v[12];
 #pragma unroll
-        for (int e = 0; e < 12; ++e)
-            v[e] = (w[e] != 0.f) ? load_feat4<T>(feat, (long long)off[e >> 2] + corner[e & 3])
-                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int e = 0; e < 12; ++e) v[e] = load_feat4(feat + off[e >> 2] + corner[e & 3]);
         const float* src = X + (lane8 * 4) * AS + q;
         const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
         float fdot = 0.f;  // <dx, f_p> restricted to this lane's channels

@@ -94,40 +94,44 @@ __device__ __forceinline__ bool part_canonical(const float* q, float x, float y,
 }
 
 // Bilinear footprint, zeros padding, align_corners=False (TriplaneSampler_kernel.cu:40-74 semantics).
+// A footprint that hangs over an edge is shifted back inside the image: the texel that moves in takes the weight 0
+// the out-of-range texel had, so all four addresses are always valid, loads need no predicate, and the result
+// is the same as with zeros padding (0 * finite adds nothing).  Requires W, H >= 2.
 struct Bilin {
-    int x0, y0;          // top-left texel (may be -1)
-    float w00, w01, w10, w11;  // weights of (y0,x0) (y0,x0+1) (y0+1,x0) (y0+1,x0+1), zero when out of range
+    int x0, y0;          // top-left texel, 0 <= x0 <= W-2, 0 <= y0 <= H-2
+    float w00, w01, w10, w11;  // weights of (y0,x0) (y0,x0+1) (y0+1,x0) (y0+1,x0+1)
 };
 
 __device__ __forceinline__ Bilin bilin_setup(float x, float y, int W, int H) {
     float ix = ((x + 1.f) * W - 1.f) * 0.5f;
     float iy = ((y + 1.f) * H - 1.f) * 0.5f;
     float fx = floorf(ix), fy = floorf(iy);
-    Bilin b;
-    b.x0 = (int)fx;
-    b.y0 = (int)fy;
+    int x0 = (int)fx, y0 = (int)fy;
     float ax = ix - fx, ay = iy - fy;
-    bool xl = b.x0 >= 0 && b.x0 < W, xr = b.x0 + 1 >= 0 && b.x0 + 1 < W;
-    bool yt = b.y0 >= 0 && b.y0 < H, yb = b.y0 + 1 >= 0 && b.y0 + 1 < H;
-    b.w00 = (xl && yt) ? (1.f - ax) * (1.f - ay) : 0.f;
-    b.w01 = (xr && yt) ? ax * (1.f - ay) : 0.f;
-    b.w10 = (xl && yb) ? (1.f - ax) * ay : 0.f;
-    b.w11 = (xr && yb) ? ax * ay : 0.f;
+    float wx0 = (x0 >= 0 && x0 < W) ? 1.f - ax : 0.f, wx1 = (x0 + 1 >= 0 && x0 + 1 < W) ? ax : 0.f;
+    float wy0 = (y0 >= 0 && y0 < H) ? 1.f - ay : 0.f, wy1 = (y0 + 1 >= 0 && y0 + 1 < H) ? ay : 0.f;
+    if (x0 < 0) { wx0 = wx1; wx1 = 0.f; }
+    if (x0 > W - 2) { wx1 = wx0; wx0 = 0.f; }
+    if (y0 < 0) { wy0 = wy1; wy1 = 0.f; }
+    if (y0 > H - 2) { wy1 = wy0; wy0 = 0.f; }
+    Bilin b;
+    b.x0 = min(max(x0, 0), W - 2);
+    b.y0 = min(max(y0, 0), H - 2);
+    b.w00 = wx0 * wy0;
+    b.w01 = wx1 * wy0;
+    b.w10 = wx0 * wy1;
+    b.w11 = wx1 * wy1;
     return b;
 }
 
 // scalar (1-channel) bilinear fetch from a row-major H x W plane
 __device__ __forceinline__ float bilin_fetch1(const float* __restrict__ plane, const Bilin& b, int W) {
-    float v = 0.f;
-    const float* r0 = plane + (ptrdiff_t)b.y0 * W + b.x0;
-    if (b.w00 != 0.f) v = fmaf(b.w00, __ldg(r0), v);
-    if (b.w01 != 0.f) v = fmaf(b.w01, __ldg(r0 + 1), v);
-    if (b.w10 != 0.f) v = fmaf(b.w10, __ldg(r0 + W), v);
-    if (b.w11 != 0.f) v = fmaf(b.w11, __ldg(r0 + W + 1), v);
-    return v;
+    const float* r0 = plane + (b.y0 * W + b.x0);
+    const float t00 = __ldg(r0), t01 = __ldg(r0 + 1), t10 = __ldg(r0 + W), t11 = __ldg(r0 + W + 1);
+    return fmaf(b.w11, t11, fmaf(b.w10, t10, fmaf(b.w01, t01, b.w00 * t00)));
 }
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + __expf(-x)); }
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.f, 1.f + __expf(-x)); }
 
 // ---- Philox4x32-10 (Salmon et al. 2011); oracle twin: enarf_oracle.philox4x32 ------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {

@@ -11,15 +11,10 @@ __device__ __forceinline__ float unit_bin(int j, int Nc, float step) {
     return (j < (Nc + 1) / 2) ? cmul(step, (float)j) : csub(1.0f, cmul(step, (float)(Nc - j)));
 }
 
-template <typename T>
-__device__ __forceinline__ float4 load_feat4(const T* base, long long elem);
-template <>
-__device__ __forceinline__ float4 load_feat4<float>(const float* base, long long elem) {
-    return __ldg(reinterpret_cast<const float4*>(base + elem));
-}
-template <>
-__device__ __forceinline__ float4 load_feat4<__nv_bfloat16>(const __nv_bfloat16* base, long long elem) {
-    uint2 r = __ldg(reinterpret_cast<const uint2*>(base + elem));
+// four consecutive channels of one texel
+__device__ __forceinline__ float4 load_feat4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float4 load_feat4(const __nv_bfloat16* p) {
+    uint2 r = __ldg(reinterpret_cast<const uint2*>(p));
     float4 v;
     v.x = __uint_as_float(r.x << 16);
     v.y = __uint_as_float(r.x & 0xffff0000u);
@@ -28,36 +23,37 @@ __device__ __forceinline__ float4 load_feat4<__nv_bfloat16>(const __nv_bfloat16*
     return v;
 }
 
-// Gather for one point by an 8-lane group: lane l owns feature channels 4l..4l+3.
+__device__ __forceinline__ void fma4(float4& f, float w, const float4& v) {
+    f.x = fmaf(w, v.x, f.x);
+    f.y = fmaf(w, v.y, f.y);
+    f.z = fmaf(w, v.z, f.z);
+    f.w = fmaf(w, v.w, f.w);
+}
+
+// f += sum over the 12 texels of one (point, part) pair record; feat already points at this lane's 4 channels.
+// All 12 loads are issued before the first FMA (the footprints are always in range: common.cuh Bilin).
 template <typename T>
-__device__ __forceinline__ float4 gather_point(const enarf_scene_t& sc, const float* s_part, int b, uint32_t m, float x,
-                                               float y, float z, int lane8) {
-    float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-    const int H = sc.H, W = sc.W;
-    const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * H * W * FEAT;
-    const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
-    while (m) {
-        const int p = __ffs(m) - 1;
-        m &= m - 1;
-        float c[3];
-        part_canonical(s_part + p * PART_STRIDE, x, y, z, c[0], c[1], c[2]);
-        Bilin bl[3];
-        float wp = 1.f;
+__device__ __forceinline__ void gather_pair(float4& f, const T* __restrict__ feat, const float* rec, int row_elems,
+                                            float scale) {
+    const float4* rp = reinterpret_cast<const float4*>(rec);
+    const float4 o4 = rp[0];
+    const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+    float4 v[12];
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
-            wp *= sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
-        }
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const long long base = ((long long)k * H * W + (long long)bl[k].y0 * W + bl[k].x0) * FEAT + lane8 * 4;
-            const float w00 = bl[k].w00 * wp, w01 = bl[k].w01 * wp, w10 = bl[k].w10 * wp, w11 = bl[k].w11 * wp;
-            float4 v;
-            if (w00 != 0.f) { v = load_feat4<T>(feat, base); f.x = fmaf(w00, v.x, f.x); f.y = fmaf(w00, v.y, f.y); f.z = fmaf(w00, v.z, f.z); f.w = fmaf(w00, v.w, f.w); }
-            if (w01 != 0.f) { v = load_feat4<T>(feat, base + FEAT); f.x = fmaf(w01, v.x, f.x); f.y = fmaf(w01, v.y, f.y); f.z = fmaf(w01, v.z, f.z); f.w = fmaf(w01, v.w, f.w); }
-            if (w10 != 0.f) { v = load_feat4<T>(feat, base + (long long)W * FEAT); f.x = fmaf(w10, v.x, f.x); f.y = fmaf(w10, v.y, f.y); f.z = fmaf(w10, v.z, f.z); f.w = fmaf(w10, v.w, f.w); }
-            if (w11 != 0.f) { v = load_feat4<T>(feat, base + (long long)(W + 1) * FEAT); f.x = fmaf(w11, v.x, f.x); f.y = fmaf(w11, v.y, f.y); f.z = fmaf(w11, v.z, f.z); f.w = fmaf(w11, v.w, f.w); }
-        }
+    for (int k = 0; k < 3; ++k) {
+        const T* p0 = feat + off[k];
+        const T* p1 = p0 + row_elems;
+        v[4 * k + 0] = load_feat4(p0);
+        v[4 * k + 1] = load_feat4(p0 + FEAT);
+        v[4 * k + 2] = load_feat4(p1);
+        v[4 * k + 3] = load_feat4(p1 + FEAT);
     }
-    return f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 w4 = rp[1 + k];
+        fma4(f, w4.x * scale, v[4 * k + 0]);
+        fma4(f, w4.y * scale, v[4 * k + 1]);
+        fma4(f, w4.z * scale, v[4 * k + 2]);
+        fma4(f, w4.w * scale, v[4 * k + 3]);
+    }
 }

@@ -290,31 +290,11 @@ __device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec
     const int lane8 = tid & 7, cnt = e - a, p0 = t.pref[a];
     const int W = sc.W;
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * sc.H * W * FEAT + lane8 * 4;
-    const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
     for (int q = tid >> 3; q < cnt; q += nthr / 8) {
         float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
         const int r1 = t.pref[a + q + 1] - p0;
-        for (int r = t.pref[a + q] - p0; r < r1; ++r) {
-            const float4* rp = reinterpret_cast<const float4*>(rec + r * REC);
-            const float4 o4 = rp[0];
-            const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
-            const float ws = SCALE ? rp[4].x : 1.f;
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float4 w4 = rp[1 + k];
-                const float w[4] = {w4.x * ws, w4.y * ws, w4.z * ws, w4.w * ws};
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    if (w[c] != 0.f) {
-                        const float4 v = load_feat4<T>(feat, (long long)off[k] + corner[c]);
-                        f.x = fmaf(w[c], v.x, f.x);
-                        f.y = fmaf(w[c], v.y, f.y);
-                        f.z = fmaf(w[c], v.z, f.z);
-                        f.w = fmaf(w[c], v.w, f.w);
-                    }
-                }
-            }
-        }
+        for (int r = t.pref[a + q] - p0; r < r1; ++r)
+            gather_pair<T>(f, feat, rec + r * REC, W * FEAT, SCALE ? rec[r * REC + 16] : 1.f);
         float* dst = X + (lane8 * 4) * AS + q;
         dst[0] = f.x;
         dst[AS] = f.y;
@@ -496,7 +476,6 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
     const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
     const int lane8 = lane & 7, grp = lane >> 3;
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * H * W * FEAT + lane8 * 4;
-    const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
     for (int q0 = 0; q0 < np;) {
         // points [q0, q1) whose pairs fit the record slab
         const int base = t.pref[a + q0];
@@ -537,26 +516,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
         for (int q = q0 + grp; q < q1; q += 4) {
             float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
             const int r1 = t.pref[a + q + 1] - base;
-            for (int r = t.pref[a + q] - base; r < r1; ++r) {
-                const float4* rp = reinterpret_cast<const float4*>(rec + r * REC);
-                const float4 o4 = rp[0];
-                const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float4 w4 = rp[1 + k];
-                    const float w[4] = {w4.x, w4.y, w4.z, w4.w};
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        if (w[c] != 0.f) {
-                            const float4 v = load_feat4<T>(feat, (long long)off[k] + corner[c]);
-                            f.x = fmaf(w[c], v.x, f.x);
-                            f.y = fmaf(w[c], v.y, f.y);
-                            f.z = fmaf(w[c], v.z, f.z);
-                            f.w = fmaf(w[c], v.w, f.w);
-                        }
-                    }
-                }
-            }
+            for (int r = t.pref[a + q] - base; r < r1; ++r) gather_pair<T>(f, feat, rec + r * REC, W * FEAT, 1.f);
             *reinterpret_cast<float4*>(X + q * XSW + ((4 * lane8) ^ (8 * (q & 3)))) = f;
         }
         __syncwarp();
