@@ -208,35 +208,42 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dfeat = a.d_feat + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dprob = a.d_prob + (size_t)b * a.d_prob_stride;
-    const int corner[4] = {0, FEAT, W * FEAT, (W + 1) * FEAT};
     for (int r = tid >> 3; r < npairs; r += NT / 8) {
         const float* rw = rec + r * REC;
         const float4* rp = reinterpret_cast<const float4*>(rw);
         const float4 o4 = rp[0];
-        const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+        const unsigned off[3] = {__float_as_uint(o4.x), __float_as_uint(o4.y), __float_as_uint(o4.z)};
         const int p = __float_as_int(o4.w) & 255, q = __float_as_int(o4.w) >> 8;
         const float wp = rp[4].x;
-        float w[12];
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float4 w4 = rp[1 + k];
-            w[4 * k] = w4.x; w[4 * k + 1] = w4.y; w[4 * k + 2] = w4.z; w[4 * k + 3] = w4.w;
-        }
         // all texel loads first (independent, always in range), then the dot products and the reductions
         float4 v[12];
 #pragma unroll
-        for (int e = 0; e < 12; ++e) v[e] = load_feat4(feat + off[e >> 2] + corner[e & 3]);
+        for (int k = 0; k < 3; ++k) {
+            const T* t0 = feat + off[k];
+            const T* t1 = t0 + W * FEAT;
+            v[4 * k + 0] = load_feat4(t0);
+            v[4 * k + 1] = load_feat4(t0 + FEAT);
+            v[4 * k + 2] = load_feat4(t1);
+            v[4 * k + 3] = load_feat4(t1 + FEAT);
+        }
         const float* src = X + (lane8 * 4) * AS + q;
         const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
-        float fdot = 0.f;  // <dx, f_p> restricted to this lane's channels
+        const float4 dxw = make_float4(dx.x * wp, dx.y * wp, dx.z * wp, dx.w * wp);
+        float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);   // this pair's raw bilinear feature, this lane's channels
 #pragma unroll
-        for (int e = 0; e < 12; ++e) {
-            if (w[e] != 0.f) {
-                fdot = fmaf(w[e], v[e].x * dx.x + v[e].y * dx.y + v[e].z * dx.z + v[e].w * dx.w, fdot);
-                const float s_ = w[e] * wp;
-                red_add_v4(dfeat + (long long)off[e >> 2] + corner[e & 3], s_ * dx.x, s_ * dx.y, s_ * dx.z, s_ * dx.w);
+        for (int k = 0; k < 3; ++k) {
+            const float4 w4 = rp[1 + k];
+            const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+            float* d0 = dfeat + off[k];
+            float* d1 = d0 + W * FEAT;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                fma4(fs, w[c], v[4 * k + c]);
+                // a zero weight (footprint shifted in at an image edge) adds 0: not worth a branch
+                red_add_v4((c >> 1 ? d1 : d0) + (c & 1) * FEAT, w[c] * dxw.x, w[c] * dxw.y, w[c] * dxw.z, w[c] * dxw.w);
             }
         }
+        float fdot = (fs.x * dx.x + fs.y * dx.y) + (fs.z * dx.z + fs.w * dx.w);   // <dx, f_p> on this lane's channels
         fdot += __shfl_xor_sync(gmask, fdot, 1);
         fdot += __shfl_xor_sync(gmask, fdot, 2);
         fdot += __shfl_xor_sync(gmask, fdot, 4);

@@ -37,7 +37,7 @@ __device__ __forceinline__ void gather_pair(float4& f, const T* __restrict__ fea
                                             float scale) {
     const float4* rp = reinterpret_cast<const float4*>(rec);
     const float4 o4 = rp[0];
-    const int off[3] = {__float_as_int(o4.x), __float_as_int(o4.y), __float_as_int(o4.z)};
+    const unsigned off[3] = {__float_as_uint(o4.x), __float_as_uint(o4.y), __float_as_uint(o4.z)};   // never negative
     float4 v[12];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
