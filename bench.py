@@ -153,7 +153,8 @@ def step_device(w, step_idx, timer=None, world=None):
     bins = timed("fine_sample", lambda: ops.fine_sample(wb, NF, seed=step_idx))
     color, mask, disp, fw, fd, pts, feat = timed("fine_fwd", lambda: ops._render_fine_fwd(
         scene, dmin, dmax, direction, bins, want_points=True, want_feat=True))
-    d_tp = torch.zeros_like(w["tri_plane"])
+    d_tp = torch.empty_like(w["tri_plane"])     # as ops.RenderFine.backward: feature channels are stored by unpack
+    d_tp[:, 96:].zero_()
     d_feat = torch.zeros(B, 3, scene.H, scene.W, 32, device=dev)
     dw = [torch.zeros_like(t) for t in scene.w]
     db = [torch.zeros_like(t) for t in scene.b]
@@ -165,7 +166,7 @@ def step_device(w, step_idx, timer=None, world=None):
             p(d_feat), d_tp[:, 96:].data_ptr(), d_tp.stride(0), p(dw[0]), p(dw[1]), p(dw[2]), p(db[0]), p(db[1]), p(db[2]),
             ops.stream_ptr()))
     timed("fine_bwd", bwd)
-    timed("unpack", lambda: ops.unpack_plane_grads(d_feat, d_tp))
+    timed("unpack", lambda: ops.unpack_plane_grads(d_feat, d_tp, accumulate=False))
     w["last"] = (color, mask, d_tp, dw, bins, dmin, dmax, direction)
     return 8   # repack, near_far, depth_range, coarse, fine_sample, fine_fwd, fine_bwd, unpack
 
@@ -200,7 +201,7 @@ class _Planes(torch.nn.Module):
         self.tp = torch.nn.Parameter(tp)
 
     def forward(self, z, bone_length, truncation_psi=1):
-        return self.tp[:z.shape[0]]
+        return self.tp if z.shape[0] == self.tp.shape[0] else self.tp[:z.shape[0]]
 
 
 def build_e2e(w, device):

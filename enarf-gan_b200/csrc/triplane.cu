@@ -23,6 +23,7 @@ __global__ void __launch_bounds__(256) repack_kernel(const float* __restrict__ s
         if (x0 + p < HW) d[(size_t)p * FEAT + tx] = (T)tile[tx][p];
 }
 
+template <bool ACC>
 __global__ void __launch_bounds__(256) unpack_grad_kernel(const float* __restrict__ d_feat, int C_total, int HW,
                                                           float* __restrict__ d_nchw) {
     __shared__ float tile[32][33];
@@ -35,7 +36,10 @@ __global__ void __launch_bounds__(256) unpack_grad_kernel(const float* __restric
     __syncthreads();
     float* d = d_nchw + ((size_t)b * C_total + k * FEAT) * HW;
     for (int c = ty; c < 32; c += 8)
-        if (x0 + tx < HW) d[(size_t)c * HW + x0 + tx] += tile[tx][c];
+        if (x0 + tx < HW) {
+            float* o = d + (size_t)c * HW + x0 + tx;
+            *o = ACC ? *o + tile[tx][c] : tile[tx][c];
+        }
 }
 
 extern "C" int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_total, int H, int W, void* feat_out,
@@ -56,14 +60,17 @@ extern "C" int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_tot
     return ENARF_OK;
 }
 
-extern "C" int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W, float* d_tri_plane_nchw,
-                                        void* stream) {
+extern "C" int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W, int accumulate,
+                                        float* d_tri_plane_nchw, void* stream) {
     ENARF_REQUIRE(d_feat && d_tri_plane_nchw && B > 0 && H > 0 && W > 0 && C_total >= 3 * FEAT, ENARF_ERR_INVALID_ARG,
                   "enarf_unpack_plane_grads: bad arguments");
     ENARF_REQUIRE(3 * B <= 65535, ENARF_ERR_UNSUPPORTED, "enarf_unpack_plane_grads: batch %d too large", B);
     const int HW = H * W;
     dim3 grid((HW + 31) / 32, 3 * B);
-    unpack_grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(d_feat, C_total, HW, d_tri_plane_nchw);
+    if (accumulate)
+        unpack_grad_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_feat, C_total, HW, d_tri_plane_nchw);
+    else
+        unpack_grad_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_feat, C_total, HW, d_tri_plane_nchw);
     ENARF_CHECK_LAUNCH("enarf_unpack_plane_grads");
     return ENARF_OK;
 }

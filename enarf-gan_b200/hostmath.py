@@ -8,9 +8,19 @@ import numpy as np
 import torch
 
 
+_PARENT_INDEX = {}   # (parent ids, device) -> index tensor; built once so the render path has no host sync
+
+
+def _parent_index(parent_id, device):
+    key = (tuple(int(p) for p in np.asarray(parent_id)[1:]), str(device))
+    if key not in _PARENT_INDEX:
+        _PARENT_INDEX[key] = torch.tensor(key[0], dtype=torch.long, device=device)
+    return _PARENT_INDEX[key]
+
+
 def part_frames(pose_to_camera, bone_length, origin_location, parent_id):
     """(B,J,4,4),(B,J-1,1) -> part frames (B,P,4,4), bone length (B,P,1)   [transform_pose]."""
-    par = torch.as_tensor(np.asarray(parent_id)[1:], dtype=torch.long, device=pose_to_camera.device)
+    par = _parent_index(parent_id, pose_to_camera.device)
     mid = (pose_to_camera[:, 1:, :, 3:] + pose_to_camera[:, par, :, 3:]) / 2
     if origin_location == "center":
         return torch.cat([pose_to_camera[:, 1:, :, :3], mid], dim=-1), bone_length

@@ -66,10 +66,10 @@ def repack_planes(tri_plane, dtype=torch.float32):
     return out
 
 
-def unpack_plane_grads(d_feat, d_tri_plane):
-    """Adds d_feat (B,3,H,W,32) into channels [0,96) of the NCHW gradient d_tri_plane."""
+def unpack_plane_grads(d_feat, d_tri_plane, accumulate=True):
+    """Adds (or, with accumulate=False, stores) d_feat (B,3,H,W,32) into channels [0,96) of the NCHW gradient."""
     B, C, H, W = d_tri_plane.shape
-    check(lib().enarf_unpack_plane_grads(ptr(d_feat), B, C, H, W, ptr(d_tri_plane), stream_ptr()))
+    check(lib().enarf_unpack_plane_grads(ptr(d_feat), B, C, H, W, int(accumulate), ptr(d_tri_plane), stream_ptr()))
     return d_tri_plane
 
 
@@ -183,9 +183,13 @@ class RenderFine(torch.autograd.Function):
         dev = bins.device
         c = lambda g: None if g is None else g.contiguous().float()
         need_tp = ctx.needs_input_grad[5]
-        d_tp = torch.zeros(ctx.tp_shape, device=dev)
+        # the feature channels of d_tp are overwritten by unpack_plane_grads: only the probability channels
+        # (scattered into directly) and the channels-last scratch need zero-filling
+        d_tp = torch.empty(ctx.tp_shape, device=dev) if need_tp else torch.zeros(ctx.tp_shape, device=dev)
         d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
         d_prob = d_tp[:, FEAT_DIM * 3:]
+        if need_tp:
+            d_prob.zero_()
         dw = [torch.zeros_like(w) for w in scene.w]
         db = [torch.zeros_like(b) for b in scene.b]
         g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
@@ -195,7 +199,7 @@ class RenderFine(torch.autograd.Function):
             ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
             ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
         if need_tp:
-            unpack_plane_grads(d_feat, d_tp)
+            unpack_plane_grads(d_feat, d_tp, accumulate=False)
         return (None, None, None, None, None, d_tp if need_tp else None, dw[0], dw[1], dw[2],
                 db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
 

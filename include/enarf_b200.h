@@ -70,8 +70,9 @@ int enarf_version(void);
  * Channel 32*k+c of the input becomes [b][k][y][x][c] (channel order of sampling.py:28). */
 int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_total, int H, int W,
                         void* feat_out, int out_dtype, void* stream);
-/* Gradient of the above: d_feat (B,3,H,W,32) fp32 is ADDED into d_tri_plane_nchw channels [0,96). */
-int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W,
+/* Gradient of the above: d_feat (B,3,H,W,32) fp32 is added into (accumulate != 0) or stored over (accumulate == 0,
+ * the destination channels may be uninitialised) d_tri_plane_nchw channels [0,96). */
+int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W, int accumulate,
                              float* d_tri_plane_nchw, void* stream);
 
 /* Batch-global near/far (rendering.py:15-17): nearfar[0] = max(min tz - sqrt3, near0),
