@@ -383,12 +383,15 @@ def main():
     dom = max(alg, key=lambda k: kt[k])
     peak, peak_src = peaks()
     achieved = alg[dom] / (kt[dom] * 1e-3) / 1e9
-    traffic = None
-    tpath = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dom)
+    traffic = traffic_src = None     # measured DRAM bytes per launch of that kernel, from the committed ncu capture
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic_r1.json")
+    if os.path.exists(tpath) and args.batch == 8:
+        tj = json.load(open(tpath))
+        if dom in tj["kernels"]:
+            traffic = tj["kernels"][dom]["dram_bytes_read"] + tj["kernels"][dom]["dram_bytes_write"]
+            traffic_src = tj["source"]
     line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                        "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                         "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kt[dom],
                         "mean_valid_parts_per_point": {"coarse": vc, "fine": vf},
                         "active_point_fraction": {"coarse": ac, "fine": af},
