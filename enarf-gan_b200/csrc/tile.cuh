@@ -1,31 +1,28 @@
 // Tile framework shared by the fused forward (render.cu) and backward (bwd.cu) kernels.
 //
-// One CTA of 512 threads (16 warps, one CTA per SM, persistent with a dynamic tile counter) owns whole rays:
-// a tile is rays x samples <= TP_MAX points.  Per tile
+// Persistent CTAs (two 256-thread CTAs per SM, dynamic tile counter) own whole rays: a tile is
+// rays x samples <= TP_MAX points.  Per tile
 //   phase 0  per (ray, part): conservative clip of the ray segment against the part cube (common.cuh);
 //   phase 1  per point: position (contract arithmetic), exact part tests on the candidates -> part mask;
 //            points inside at least one part are compacted into `list`; a prefix sum of popc(mask) over
 //            the list gives every active point its range of (point, part) pairs;
-//   chunks   <= CH active points and <= PB pairs at a time:
-//     setup    ONE thread per (point, part) pair: canonical coordinates, three bilinear footprints, the
-//              twelve probability texels, sigmoid product -> a 20-word record in shared memory
-//              (the old kernels redid this on each of the 8 lanes that gather a point);
-//     gather   8 lanes per point walk the point's records: 12 x 128-bit texel loads per pair, lane l owns
-//              channels 4l..4l+3; features land in X[channel][point];
-//     decoder  register-tiled FP32 GEMMs over the chunk (4 points x 4 outputs per thread), activations
-//              stay in shared memory as [channel][point] rows of stride AS.
-// Why FP32 FFMA and not tensor cores: the parity bar is 1e-4 on fp32 outputs; measured on B200
-// (profiles/mma_rate_r1.txt) mma.sync tf32 issues 139 TMAC/s and bf16 278 TMAC/s against 36 TMAC/s of FFMA, so an
-// error-compensated 3xTF32 / 6xBF16 split lands at ~46 TMAC/s -- no better than FFMA once the split and
-// fragment shuffles are paid.
+//   pair records  ONE thread (lane) per (point, part) pair: canonical coordinates, three bilinear footprints,
+//            the twelve probability texels, sigmoid product -> a 20-word record in shared memory;
+//   gather   8 lanes per point walk the point's records: 12 x 128-bit texel loads per pair, lane l owns
+//            channels 4l..4l+3.
+// The forward consumes chunks of 32 active points per WARP (gather32_warp below, decoder in mlp_mma.cuh), the
+// backward chunks of <= CH points per CTA (setup_pairs / gather_chunk below, GEMMs in mma_smem.cuh) with
+// activations as [channel][point] rows of stride AS.  Both run the decoder as error-compensated 3xTF32
+// mma.sync (see mlp_mma.cuh for the measured trade-off against FFMA).
 #pragma once
 #include <cuda_bf16.h>
 
 #include "common.cuh"
 #include "gather.cuh"
 
-// Geometry of the CTA; a translation unit may pre-define these before including this header (bwd.cu runs two
-// 256-thread CTAs per SM on 64-point chunks, render.cu one 512-thread CTA per SM).
+// Geometry of the CTA; a translation unit pre-defines these before including this header (render.cu and bwd.cu both
+// run two 256-thread CTAs per SM; bwd.cu adds 64-point CTA-wide chunks).  The defaults below are the one-CTA-per-SM
+// geometry of the earlier versions and still compile.
 #ifndef NT
 #define NT 512             // threads per CTA
 #endif
@@ -309,85 +306,6 @@ __device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec
     }
 }
 
-// ---- register-tiled FP32 GEMMs over one chunk ---------------------------------------------------------
-// Thread tile: 4 consecutive points (quad pq) x 4 outputs.  acc[p][j].
-// (1) weights stored [out][k] (k contiguous): out rows og + 16 j, four k per step.
-template <int K, int WS>
-__device__ __forceinline__ void gemm_kvec(const float* __restrict__ act, const float* __restrict__ Wm, int pq, int og,
-                                          float (&acc)[4][4]) {
-#pragma unroll 2
-    for (int k = 0; k < K; k += 4) {
-        float4 w[4], x[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) w[j] = *reinterpret_cast<const float4*>(Wm + (og + 16 * j) * WS + k);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * pq);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                acc[0][j] = fmaf(x[i].x, wj[i], acc[0][j]);
-                acc[1][j] = fmaf(x[i].y, wj[i], acc[1][j]);
-                acc[2][j] = fmaf(x[i].z, wj[i], acc[2][j]);
-                acc[3][j] = fmaf(x[i].w, wj[i], acc[3][j]);
-            }
-        }
-    }
-}
-
-// (2) weights stored [k][in] (in contiguous): out[pt][i0+i] = sum_k G[k][pt] * Wm[k][i0+i], NI = 4 or 2.
-template <int K, int WS, int NI>
-__device__ __forceinline__ void gemm_kmajor(const float* __restrict__ G, const float* __restrict__ Wm, int pq, int i0,
-                                            float (&acc)[4][NI]) {
-#pragma unroll 4
-    for (int k = 0; k < K; ++k) {
-        const float4 g = *reinterpret_cast<const float4*>(G + k * AS + 4 * pq);
-        float w[NI];
-        if (NI == 4) {
-            const float4 v = *reinterpret_cast<const float4*>(Wm + k * WS + i0);
-            w[0] = v.x; w[1] = v.y; w[NI - 2] = v.z; w[NI - 1] = v.w;
-        } else {
-            const float2 v = *reinterpret_cast<const float2*>(Wm + k * WS + i0);
-            w[0] = v.x; w[1] = v.y;
-        }
-#pragma unroll
-        for (int i = 0; i < NI; ++i) {
-            acc[0][i] = fmaf(g.x, w[i], acc[0][i]);
-            acc[1][i] = fmaf(g.y, w[i], acc[1][i]);
-            acc[2][i] = fmaf(g.z, w[i], acc[2][i]);
-            acc[3][i] = fmaf(g.w, w[i], acc[3][i]);
-        }
-    }
-}
-
-// (3) weight gradient: acc[j][jj] += sum over quads q = h, h+KS, ... < nquads of
-//     G[ot + 16 j][4q..4q+3] . A[it + IS jj][4q..4q+3]
-template <int KS, int IS>
-__device__ __forceinline__ void wgrad_tile(const float* __restrict__ G, const float* __restrict__ A, int ot, int it,
-                                           int h, int nquads, float (&acc)[4][4], float (&bsum)[4]) {
-    for (int q = h; q < nquads; q += KS) {
-        float4 g[4], x[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) g[j] = *reinterpret_cast<const float4*>(G + (ot + 16 * j) * AS + 4 * q);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) x[j] = *reinterpret_cast<const float4*>(A + (it + IS * j) * AS + 4 * q);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-#pragma unroll
-            for (int jj = 0; jj < 4; ++jj) {
-                float s = acc[j][jj];
-                s = fmaf(g[j].x, x[jj].x, s);
-                s = fmaf(g[j].y, x[jj].y, s);
-                s = fmaf(g[j].z, x[jj].z, s);
-                s = fmaf(g[j].w, x[jj].w, s);
-                acc[j][jj] = s;
-            }
-            if (it == 0) bsum[j] += (g[j].x + g[j].y) + (g[j].z + g[j].w);
-        }
-    }
-}
-
 // Decoder head (64 -> 4) with four lanes per point: lane kq sums the hidden units kq, kq+4, ...; after two
 // shuffles every one of the four lanes holds o3[c] = sum_k A2[k][pt] W3[c][k] + b3[c].  All 32 lanes of the
 // warp must call it (points 8*warp .. 8*warp+7).
@@ -409,56 +327,6 @@ __device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& 
         o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 1);
         o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 2);
         o3[c] += d.b3[c];
-    }
-}
-
-// ---- named barriers (id 0 is __syncthreads) -------------------------------------------------------------
-__device__ __forceinline__ void bar_sync(int id, int nthreads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-__device__ __forceinline__ void bar_arrive(int id, int nthreads) {
-    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
-}
-
-// (1b) as gemm_kvec but 8 points per thread: quads q0 and q1 (q1 skipped when !two); acc[2][4][4] = [quad][p][j]
-template <int K, int WS>
-__device__ __forceinline__ void gemm_kvec2(const float* __restrict__ act, const float* __restrict__ Wm, int q0, int q1,
-                                           bool two, int og, float (&acc)[2][4][4]) {
-#pragma unroll 2
-    for (int k = 0; k < K; k += 4) {
-        float4 w[4], x[4], y[4];
-#pragma unroll
-        for (int j = 0; j < 4; ++j) w[j] = *reinterpret_cast<const float4*>(Wm + (og + 16 * j) * WS + k);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) x[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * q0);
-        if (two) {
-#pragma unroll
-            for (int i = 0; i < 4; ++i) y[i] = *reinterpret_cast<const float4*>(act + (k + i) * AS + 4 * q1);
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                acc[0][0][j] = fmaf(x[i].x, wj[i], acc[0][0][j]);
-                acc[0][1][j] = fmaf(x[i].y, wj[i], acc[0][1][j]);
-                acc[0][2][j] = fmaf(x[i].z, wj[i], acc[0][2][j]);
-                acc[0][3][j] = fmaf(x[i].w, wj[i], acc[0][3][j]);
-            }
-        }
-        if (two) {
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const float wj[4] = {w[j].x, w[j].y, w[j].z, w[j].w};
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    acc[1][0][j] = fmaf(y[i].x, wj[i], acc[1][0][j]);
-                    acc[1][1][j] = fmaf(y[i].y, wj[i], acc[1][1][j]);
-                    acc[1][2][j] = fmaf(y[i].z, wj[i], acc[1][2][j]);
-                    acc[1][3][j] = fmaf(y[i].w, wj[i], acc[1][3][j]);
-                }
-            }
-        }
     }
 }
 
