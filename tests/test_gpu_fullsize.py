@@ -1,0 +1,141 @@
+"""Size-independent properties of the fused path at BASELINE.json's full per-sample size (128x128 rays, 48+48
+samples per ray, 24 parts), where the CPU oracle is too slow to be the checker:
+compositing identities, ray validity, sortedness of the fine samples, batch independence (bit-exact), ray-chunk
+invariance (bit-exact), and linearity / additivity of the backward."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SIZE, NC, NF = 128, 48, 48
+
+
+def _scene(B, seed=1236, requires_grad=False):
+    from enarf_gan_b200 import hostmath, rendering, synthetic as S
+    dev = torch.device("cuda:0")
+    inp = S.make_inputs(B, SIZE, seed=seed)
+    tp = S.make_triplane(B, seed=seed).to(dev)
+    scene = hostmath.random_scene(inp, tp, seed=seed, device=dev)
+    img = rendering.pixel_grid(SIZE, SIZE, B, dev)
+    return scene, img, inp["inv_intrinsics"].to(dev), tp
+
+
+def _render(scene, img, invK, **kw):
+    from enarf_gan_b200 import rendering
+    return rendering.render_rays(scene, img, invK, NC, NF, rng="philox", seed=7, return_intermediate=True, **kw)
+
+
+def test_compositing_identities_and_validity():
+    scene, img, invK, _ = _scene(2)
+    out = _render(scene, img, invK)
+    fw, mask, color, disp = out["fine_weights"], out["mask"], out["color"], out["disparity"]
+    assert fw.shape == (2, SIZE * SIZE, NF - 1)
+    assert torch.isfinite(color).all() and torch.isfinite(disp).all()
+    # depth = dmin*(1-u) + dmax*u is evaluated as the reference does (rendering.py:198-206), so two nearly equal
+    # sorted u can give depths one ulp out of order and a weight of -sigma*ulp(depth) ~ -1e-5: bounded, not clamped
+    assert fw.min().item() > -1e-4
+    # mask = sum of the per-sample weights; transmittance keeps it in [0, 1]
+    assert (fw.sum(-1) - mask).abs().max().item() < 1e-5
+    assert mask.min().item() >= -1e-4 and mask.max().item() <= 1 + 1e-5
+    # |rgb| <= 1 per sample (tanh) -> |colour| <= mask
+    assert (color.abs() <= mask[:, None] + 1e-5).all()
+    # B > 1: rays whose 32 depth probes miss every part keep the fallback [near, far] range and are still rendered
+    # (rendering.py:60-79), so only the B == 1 compaction guarantees zeros for them (rendering.py:337-350)
+    miss = ~out["validity"]
+    assert miss.any() and (~miss).any()
+    s1, img1, invK1, _ = _scene(1)
+    o1 = _render(s1, img1, invK1)
+    m1 = ~o1["validity"]
+    assert m1.any() and (o1["mask"][m1] == 0).all() and (o1["color"].permute(0, 2, 1)[m1] == 0).all()
+    assert o1["fine_weights"].shape[1] == int((~m1).sum())
+    # disparity = sum w / depth, depth inside [depth_min, depth_max]
+    fd = out["fine_depth"]
+    lo = (fw / fd[..., :-1].clamp_min(1e-6)).sum(-1)
+    assert (disp - lo).abs().max().item() < 1e-4
+
+
+def test_fine_samples_sorted_and_in_range():
+    scene, img, invK, _ = _scene(2)
+    out = _render(scene, img, invK)
+    bins, fd = out["bins"], out["fine_depth"]
+    assert bins.shape == (2, SIZE * SIZE, NF)
+    assert (bins >= 0).all() and (bins <= 1).all()
+    assert (bins[..., 1:] >= bins[..., :-1]).all()
+    assert (fd[..., 1:] - fd[..., :-1]).min().item() > -1e-5   # see the note on one-ulp inversions above
+    dmin, dmax = out["depth_min"], out["depth_max"]
+    assert (fd >= dmin[..., None] - 1e-5).all() and (fd <= dmax[..., None] + 1e-5).all()
+    # the blurred coarse weights are a strictly positive distribution seed (+0.01 floor, rendering.py:187-190)
+    assert out["coarse_weights_blurred"].min().item() >= 0.01 - 1e-7
+
+
+def test_batch_independence_bit_exact():
+    """Sample b of a batched render equals the same sample rendered alone (same batch-global near/far)."""
+    from enarf_gan_b200 import ops
+    scene, img, invK, tp = _scene(3)
+    nearfar = ops.near_far(scene.pose)
+    full = _render(scene, img, invK, nearfar=nearfar, compact_b1=False)
+    for b in (0, 2):
+        one = ops.SceneBuffers(scene.pose[b:b + 1].contiguous(), scene.cscale[b:b + 1].contiguous(), scene.canon_pose,
+                               tp[b:b + 1].contiguous(), [(w[b:b + 1].contiguous(), bias) for w, bias in zip(scene.w, scene.b)])
+        out = _render(one, img[b:b + 1].contiguous(), invK[b:b + 1].contiguous(), nearfar=nearfar, compact_b1=False)
+        # the Philox counter is the launch ray index, so the jitter differs between the two launches: compare the
+        # deterministic stages exactly and the composited outputs on the coarse stage only
+        assert torch.equal(out["depth_min"][0], full["depth_min"][b])
+        assert torch.equal(out["validity"][0], full["validity"][b])
+        assert torch.equal(out["coarse_weights_blurred"][0], full["coarse_weights_blurred"][b])
+
+
+def test_ray_chunk_invariance_bit_exact():
+    """Rendering a sample's rays in chunks gives exactly the one-launch result when the fine samples are the same."""
+    from enarf_gan_b200 import ops
+    scene, img, invK, _ = _scene(1)
+    nearfar = ops.near_far(scene.pose)
+    dmin, dmax, direction, valid = ops.depth_range(img, invK, scene.pose, nearfar)
+    wb = ops.render_coarse(scene, dmin, dmax, direction, NC)
+    bins = ops.fine_sample(wb, NF, seed=3)
+    ref = ops.render_fine(scene, dmin, dmax, direction, bins)
+    n = dmin.shape[1]
+    for chunk in (4096, 1000):
+        parts = []
+        for s in range(0, n, chunk):
+            e = min(n, s + chunk)
+            wb_c = ops.render_coarse(scene, dmin[:, s:e].contiguous(), dmax[:, s:e].contiguous(),
+                                     direction[:, :, s:e].contiguous(), NC)
+            assert torch.equal(wb_c, wb[:, s:e])
+            parts.append(ops.render_fine(scene, dmin[:, s:e].contiguous(), dmax[:, s:e].contiguous(),
+                                         direction[:, :, s:e].contiguous(), bins[:, s:e].contiguous()))
+        color = torch.cat([p[0] for p in parts], dim=2)
+        mask = torch.cat([p[1] for p in parts], dim=1)
+        fw = torch.cat([p[3] for p in parts], dim=1)
+        assert torch.equal(color, ref[0]) and torch.equal(mask, ref[1]) and torch.equal(fw, ref[3])
+
+
+def test_backward_is_positively_homogeneous():
+    """For a fixed forward the backward is linear in the upstream gradient except for MyReLU, whose backward
+    (NeRF/activation.py:12-16) depends on the SIGN of the incoming gradient: so d(a*g) == a*d(g) must hold for
+    a > 0 (and only then).  Tolerance covers the non-deterministic order of the floating-point reductions."""
+    from enarf_gan_b200 import ops
+    scene, img, invK, tp = _scene(1)
+    nearfar = ops.near_far(scene.pose)
+    dmin, dmax, direction, valid = ops.depth_range(img, invK, scene.pose, nearfar)
+    wb = ops.render_coarse(scene, dmin, dmax, direction, NC)
+    bins = ops.fine_sample(wb, NF, seed=11)
+    n = dmin.shape[1]
+    gen = torch.Generator(device="cuda").manual_seed(3)
+    gc, gm = torch.randn(1, 3, n, device="cuda", generator=gen), torch.randn(1, n, device="cuda", generator=gen)
+
+    def grads(gc, gm):
+        tp_g = tp.clone().requires_grad_()
+        dec = [(w.clone().requires_grad_(), b.clone().requires_grad_()) for w, b in zip(scene.w, scene.b)]
+        sc = ops.SceneBuffers(scene.pose, scene.cscale, scene.canon_pose, tp_g, dec)
+        color, mask, *_ = ops.render_fine(sc, dmin, dmax, direction, bins, tri_plane=tp_g, decoder=dec)
+        ((color * gc).sum() + (mask * gm).sum()).backward()
+        return [tp_g.grad] + [t.grad for pair in dec for t in pair]
+
+    a = 2.5
+    g1, ga = grads(gc, gm), grads(a * gc, a * gm)
+    for x, z in zip(g1, ga):
+        assert (z - a * x).abs().max().item() <= 2e-4 * (a * x).abs().max().item() + 1e-7
+    assert g1[0].abs().max().item() > 0
+    # the feature-plane gradient only touches texels, the probability-plane gradient only the 3*P part channels
+    assert torch.isfinite(g1[0]).all()
