@@ -3,11 +3,11 @@
 // Reference being replaced: libraries/NeRF/rendering.py:119-335, models/narf.py:147-275,
 // libraries/triplane/sampling.py:54-127, libraries/triplane/triplane_nerf.py:32-48.
 //
-// One 512-thread CTA per SM owns whole rays (tile.cuh: phase 0/1, compaction, pair prefix).  Inside a tile the
-// 16 warps are autonomous: each pulls chunks of 32 active points from a shared-memory counter and, with no
+// Two 256-thread CTAs per SM, each owning whole rays (tile.cuh: phase 0/1, compaction, pair prefix).  Inside a tile
+// the 8 warps are autonomous: each pulls chunks of 32 active points from a shared-memory counter and, with no
 // CTA-wide barrier,
 //   sets up the (point, part) pair records of its points (one lane per pair), gathers the features with 8 lanes
-//   per point into its own 5 KB slab, and runs the 32->64->64->4 decoder for its 32 points on the tensor pipe
+//   per point into its own 4 KB slab, and runs the 32->64->64->4 decoder for its 32 points on the tensor pipe
 //   (mlp_mma.cuh: error-compensated 3xTF32 mma.sync, activations chained through registers),
 // so that the latency-bound gathers of some warps overlap the tensor work of others.  Then one warp per ray
 // composites: shuffle scan of sigma*delta -> transmittance -> weights -> colour/mask/disparity.

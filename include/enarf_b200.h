@@ -85,6 +85,8 @@ int enarf_depth_range(const float* image_coord, const float* inv_K, const float*
                       int B, int P, int n, float* depth_min, float* depth_max, float* ray_dir,
                       uint8_t* validity, void* stream);
 
+/* Limits of the fused passes below: 2 <= Nc, Nf <= 512 samples per ray, P <= 32 parts, H, W >= 2
+ * (ENARF_ERR_UNSUPPORTED / ENARF_ERR_INVALID_ARG otherwise). */
 /* Coarse pass (rendering.py:119-190 + narf.py:176-275, no gradient): Nc stratified mid-points per ray ->
  * density -> alpha weights -> max-blur + 0.01.  weights_out (B,n,Nc); density_out (B,n,Nc) optional (NULL). */
 int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
