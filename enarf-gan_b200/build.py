@@ -16,6 +16,7 @@ OBJ_DIR = os.path.join(PKG, "csrc", "build")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--use_fast_math=false"]
 NVCC_FLAGS = [f for f in NVCC_FLAGS if not f.startswith("--use_fast_math")]
+NVCC_FLAGS += os.environ.get("ENARF_NVCC_EXTRA", "").split()   # development builds, e.g. -DENARF_PHASE_TIMING
 
 
 def _nvcc():

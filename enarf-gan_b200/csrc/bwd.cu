@@ -63,6 +63,25 @@ struct __align__(16) BwdSmem {
     float db3[4];
 };
 
+#ifdef ENARF_PHASE_TIMING   // development build: per-phase clock64() sums of thread 0 of every CTA
+__device__ unsigned long long g_bwd_phase[16];
+#define PHASE_DECL long long ph_t = clock64(); unsigned long long ph_acc[16] = {}
+#define PHASE(i) do { if (tid == 0) { const long long now_ = clock64(); ph_acc[i] += (unsigned long long)(now_ - ph_t); ph_t = now_; } } while (0)
+#define PHASE_FLUSH do { if (tid == 0) for (int i_ = 0; i_ < 16; ++i_) atomicAdd(&g_bwd_phase[i_], ph_acc[i_]); } while (0)
+extern "C" int enarf_debug_bwd_phases(unsigned long long* host_out, int reset) {
+    cudaMemcpyFromSymbol(host_out, g_bwd_phase, sizeof(g_bwd_phase));
+    if (reset) {
+        unsigned long long z[16] = {};
+        cudaMemcpyToSymbol(g_bwd_phase, z, sizeof(z));
+    }
+    return 0;
+}
+#else
+#define PHASE_DECL
+#define PHASE(i)
+#define PHASE_FLUSH
+#endif
+
 __device__ __forceinline__ float act_grad(float a) { return (a > 0.f ? 1.f : 0.2f) * 1.4142135623730951f; }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -229,20 +248,24 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
         const float* src = X + (lane8 * 4) * AS + q;
         const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
         const float4 dxw = make_float4(dx.x * wp, dx.y * wp, dx.z * wp, dx.w * wp);
-        float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);   // this pair's raw bilinear feature, this lane's channels
+        // the reductions depend only on the weights and dX: they are issued while the texel loads are still in flight
+        float w[12];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             const float4 w4 = rp[1 + k];
-            const float w[4] = {w4.x, w4.y, w4.z, w4.w};
+            w[4 * k] = w4.x; w[4 * k + 1] = w4.y; w[4 * k + 2] = w4.z; w[4 * k + 3] = w4.w;
             float* d0 = dfeat + off[k];
             float* d1 = d0 + W * FEAT;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
-                fma4(fs, w[c], v[4 * k + c]);
                 // a zero weight (footprint shifted in at an image edge) adds 0: not worth a branch
-                red_add_v4((c >> 1 ? d1 : d0) + (c & 1) * FEAT, w[c] * dxw.x, w[c] * dxw.y, w[c] * dxw.z, w[c] * dxw.w);
+                const float wc = w[4 * k + c];
+                red_add_v4((c >> 1 ? d1 : d0) + (c & 1) * FEAT, wc * dxw.x, wc * dxw.y, wc * dxw.z, wc * dxw.w);
             }
         }
+        float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);   // this pair's raw bilinear feature, this lane's channels
+#pragma unroll
+        for (int e = 0; e < 12; ++e) fma4(fs, w[e], v[e]);
         float fdot = (fs.x * dx.x + fs.y * dx.y) + (fs.z * dx.z + fs.w * dx.w);   // <dx, f_p> on this lane's channels
         fdot += __shfl_xor_sync(gmask, fdot, 1);
         fdot += __shfl_xor_sync(gmask, fdot, 2);
@@ -273,9 +296,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
     WGrad wg;
     wgrad_zero(wg);
     if (tid < 4) s.db3[tid] = 0.f;
+    PHASE_DECL;
 
     for (;;) {
         __syncthreads();  // everyone is done with the previous tile (and with s.t.tile)
+        PHASE(15);
         if (tid == 0) s.t.tile = atomicAdd(a.tile_counter, 1);
         __syncthreads();
         const int tile = s.t.tile;
@@ -306,8 +331,10 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         __syncthreads();
 
         // ---- 1. positions, masks, compaction (identical arithmetic to the forward) -----------------
+        PHASE(0);   // tile load
         tile_points<TILE_FINE>(s.t, s.r, s.part, a.g, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
+        PHASE(1);   // tile_points
 
         // ---- 2. compositing backward, one warp per ray, in place on pg ------------------------------
         float* pgf = reinterpret_cast<float*>(s.pg);
@@ -365,34 +392,51 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             if (lane == 0) *reinterpret_cast<float4*>(go + M * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         __syncthreads();
+        PHASE(2);   // composite backward
 
         // ---- 3. per chunk: records -> gather -> decoder forward -> decoder backward -> scatter -------
         for (int c0 = 0; c0 < n_active;) {
             const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
             const int cend = (cnt + 31) & ~31;
             const bool tile_on = 32 * m.pb < cnt;   // this warp's 32 points intersect the chunk
-            setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
-            if (a.feat) {   // features checkpointed by the forward: 8 lanes per point, one 128-B row each
+            // features checkpointed by the forward: 8 lanes per point, one 128-B row each.  The loads are issued
+            // before the pair set-up (itself bound by the latency of its probability texels) and stored after it.
+            static_assert(CH == 2 * (NT / 8), "two checkpoint rows per 8-lane group");
+            float4 fx[2];
+            const int l8 = tid & 7;
+            if (a.feat) {
                 const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
-                const int l8 = tid & 7;
-                for (int q = tid >> 3; q < cend; q += NT / 8) {
-                    const float4 f = q < cnt ? __ldg(fi + (size_t)s.t.list[c0 + q] * (FEAT / 4) + l8)
-                                             : make_float4(0.f, 0.f, 0.f, 0.f);
-                    float* dst = s.X + (l8 * 4) * AS + q;
-                    dst[0] = f.x;
-                    dst[AS] = f.y;
-                    dst[2 * AS] = f.z;
-                    dst[3 * AS] = f.w;
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int q = (tid >> 3) + i * (NT / 8);
+                    fx[i] = q < cnt ? __ldg(fi + (size_t)s.t.list[c0 + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
+            if (a.feat) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int q = (tid >> 3) + i * (NT / 8);
+                    if (q < cend) {
+                        float* dst = s.X + (l8 * 4) * AS + q;
+                        dst[0] = fx[i].x;
+                        dst[AS] = fx[i].y;
+                        dst[2 * AS] = fx[i].z;
+                        dst[3 * AS] = fx[i].w;
+                    }
                 }
             } else {
                 __syncthreads();
                 gather_chunk<T, true>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
             }
             __syncthreads();
+            PHASE(3);   // records + X load
             if (tile_on) decoder_layer<FEAT>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
+            PHASE(4);   // L1
             if (tile_on) decoder_layer<HID>(s.A1, s.dec.w2, W2S, s.dec.b2, s.A2, m);
             __syncthreads();
+            PHASE(5);   // L2
             if (8 * warp < cend) {   // head forward + backward: four lanes per point, lane c owns output c
                 const int pt = tid >> 2, c = tid & 3;
                 float o3[4];
@@ -421,6 +465,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 if (lane < 4) atomicAdd(&s.db3[c], v);
             }
             __syncthreads();
+            PHASE(6);   // head
             if (tile_on) {   // G2 = (W3^T g3) * act'(a2), in place over A2; dW3 partial sums
                 float4 g3[4];
 #pragma unroll
@@ -446,9 +491,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
+            PHASE(7);   // G2 pass
             // dW2 += G2^T A1 over the chunk's points: warp tile rows (o) 16 wr.., cols (i) 8 TN2 wc..
             wgrad_mma<TN2>(s.A2, s.A1, 16 * m.wr, 8 * TN2 * m.wc, cend, m.g, m.t, wg.w2);
             __syncthreads();
+            PHASE(8);   // dW2
             if (tile_on) {   // G1 = (G2 W2) * act'(a1), in place over A1; db1 partial sums
                 float acc[2][2][4];
                 gemm_pts_mma<HID, 2, true>(s.A2, s.dec.w2, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
@@ -470,9 +517,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
+            PHASE(9);   // G1
             // dW1 += G1^T X: warp tile rows (o) 16 wr.., cols (c) 8 TN1 wc..
             wgrad_mma<TN1>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
             __syncthreads();
+            PHASE(10);  // dW1
             if (tile_on) {   // dX = G1 W1, in place over X: warp tile points 32 pb.., channels 8 ob..
                 float acc[2][1][4];
                 gemm_pts_mma<HID, 1, true>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
@@ -487,12 +536,16 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
+            PHASE(11);  // dX
             scatter_chunk<T>(s.t, s.r.rec, s.X, a, b, c0, c1, tid);
             __syncthreads();
+            PHASE(12);  // scatter
             c0 = c1;
         }
     }
     if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
+    PHASE(13);
+    PHASE_FLUSH;
 }
 
 extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
