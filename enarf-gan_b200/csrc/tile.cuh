@@ -188,12 +188,16 @@ __device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float
         }
         const uint32_t bal = __ballot_sync(0xffffffffu, m != 0);
         if (lane == 0) t.act[i >> 5] = bal;
-        if (bal) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(&t.n_active, __popc(bal));
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (m) t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)i;
-        }
+    }
+    __syncthreads();
+    // compaction in point order (deterministic: the forward and the backward of a tile see the same list, and a
+    // chunk's points are consecutive along their rays): block b of 32 points starts at the popcount of the blocks before
+    for (int i = tid; i < ((tp + 31) & ~31); i += NT) {
+        const uint32_t bal = t.act[i >> 5];
+        int base = 0;
+        for (int k = 0; k < (i >> 5); ++k) base += __popc(t.act[k]);
+        if ((bal >> lane) & 1) t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)i;
+        if (i + 32 >= ((tp + 31) & ~31) && lane == 0) t.n_active = base + __popc(bal);   // the last block closes the count
     }
     __syncthreads();
     // exclusive prefix of pairs-per-point over the active list (2 entries per thread)
