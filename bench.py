@@ -151,8 +151,8 @@ def step_device(w, step_idx, timer=None, world=None):
     dmin, dmax, direction, valid = timed("depth_range", lambda: ops.depth_range(w["img"], w["inv_K"], w["pose"], nearfar))
     wb = timed("coarse", lambda: ops.render_coarse(scene, dmin, dmax, direction, NC))
     bins = timed("fine_sample", lambda: ops.fine_sample(wb, NF, seed=step_idx))
-    color, mask, disp, fw, fd, pts, feat = timed("fine_fwd", lambda: ops._render_fine_fwd(
-        scene, dmin, dmax, direction, bins, want_points=True, want_feat=True))
+    color, mask, disp, fw, fd, pts, feat, pairs = timed("fine_fwd", lambda: ops._render_fine_fwd(
+        scene, dmin, dmax, direction, bins, want_points=True, want_feat=True, want_pairs=True))
     d_tp = torch.empty_like(w["tri_plane"])     # as ops.RenderFine.backward: feature channels are stored by unpack
     d_tp[:, 96:].zero_()
     d_feat = torch.zeros(B, 3, scene.H, scene.W, 32, device=dev)
@@ -162,7 +162,8 @@ def step_device(w, step_idx, timer=None, world=None):
 
     def bwd():
         ops.check(ops.lib().enarf_render_fine_bwd(
-            scene.ref, p(dmin), p(dmax), p(direction), p(bins), p(pts), p(feat), n, NF, p(w["g_color"]), p(w["g_mask"]), None, None,
+            scene.ref, p(dmin), p(dmax), p(direction), p(bins), p(pts), p(feat), pairs.ref, n, NF, p(w["g_color"]), p(w["g_mask"]),
+            None, None,
             p(d_feat), d_tp[:, 96:].data_ptr(), d_tp.stride(0), p(dw[0]), p(dw[1]), p(dw[2]), p(db[0]), p(db[1]), p(db[2]),
             ops.stream_ptr()))
     timed("fine_bwd", bwd)

@@ -25,6 +25,12 @@ class Scene(ctypes.Structure):
     ]
 
 
+class PairCkpt(ctypes.Structure):
+    """Mirror of enarf_pair_ckpt_t."""
+    _fields_ = [("rec", c_void_p), ("feat", c_void_p), ("tile_base", c_void_p), ("cursor", c_void_p),
+                ("capacity", c_int64)]
+
+
 _P = c_void_p
 _SIGNATURES = {
     "enarf_last_error": (c_char_p, []),
@@ -35,8 +41,10 @@ _SIGNATURES = {
     "enarf_depth_range": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
     "enarf_render_coarse": (c_int, [POINTER(Scene), _P, _P, _P, c_int, c_int, _P, _P, _P]),
     "enarf_fine_sample": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, c_uint64, c_int64, _P, _P, _P]),
-    "enarf_render_fine_fwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, _P, _P]),
-    "enarf_render_fine_bwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P,
+    "enarf_fine_tiles_per_sample": (c_int, [c_int, c_int]),
+    "enarf_render_fine_fwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, _P,
+                                      POINTER(PairCkpt), _P]),
+    "enarf_render_fine_bwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, _P, _P, POINTER(PairCkpt), c_int, c_int, _P, _P, _P, _P,
                                       _P, _P, c_int64, _P, _P, _P, _P, _P, _P, _P]),
     "enarf_density_query": (c_int, [POINTER(Scene), _P, c_int, _P, _P, _P, _P]),
     "enarf_triplane_sample_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,

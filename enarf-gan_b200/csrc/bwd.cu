@@ -37,6 +37,7 @@ struct BwdArgs {
     TileGeom g;
     const float* saved;       // (B,n,S,4)
     const float* feat;        // (B,n,S,32) forward's feature checkpoint | NULL (gather again)
+    enarf_pair_ckpt_t ck;     // forward's per-pair checkpoint (rec == NULL: none)
     const float* g_color;     // (B,3,n) | NULL
     const float* g_mask;      // (B,n)   | NULL
     const float* g_disp;      // (B,n)   | NULL
@@ -217,9 +218,12 @@ __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm,
 
 // Scatter for the chunk [c0, c1): 8 lanes per (point, part) PAIR -- pairs are independent here, so the work
 // is spread evenly over the 64 groups whatever the number of parts per point; lane l owns channels 4l..4l+3.
-template <typename T>
+// CK: the records come from the forward's pair checkpoint (weights already multiplied by the part weight, word 3 =
+// part | active index << 8, word 16 = 1 / part weight) and ck_feat points at the chunk's first checkpointed pair
+// feature, which replaces the 12 texel loads: <dX, f_p> = <dX, wp f_p> / wp.
+template <typename T, bool CK>
 __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* rec, const float* X, const BwdArgs& a,
-                                              int b, int c0, int c1, int tid) {
+                                              int b, int c0, int c1, int tid, const float* __restrict__ ck_feat) {
     const enarf_scene_t& sc = a.sc;
     const int lane8 = tid & 7, npairs = t.pref[c1] - t.pref[c0];
     const int H = sc.H, W = sc.W, HW = H * W;
@@ -232,22 +236,26 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
         const float4* rp = reinterpret_cast<const float4*>(rw);
         const float4 o4 = rp[0];
         const unsigned off[3] = {__float_as_uint(o4.x), __float_as_uint(o4.y), __float_as_uint(o4.z)};
-        const int p = __float_as_int(o4.w) & 255, q = __float_as_int(o4.w) >> 8;
-        const float wp = rp[4].x;
+        const int p = __float_as_int(o4.w) & 255, q = (__float_as_int(o4.w) >> 8) - (CK ? c0 : 0);
+        const float wp = rp[4].x;   // CK: 1 / part weight
         // all texel loads first (independent, always in range), then the dot products and the reductions
-        float4 v[12];
+        float4 v[CK ? 1 : 12];
+        if (CK) {
+            v[0] = __ldg(reinterpret_cast<const float4*>(ck_feat + (size_t)r * FEAT + 4 * lane8));
+        } else {
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const T* t0 = feat + off[k];
-            const T* t1 = t0 + W * FEAT;
-            v[4 * k + 0] = load_feat4(t0);
-            v[4 * k + 1] = load_feat4(t0 + FEAT);
-            v[4 * k + 2] = load_feat4(t1);
-            v[4 * k + 3] = load_feat4(t1 + FEAT);
+            for (int k = 0; k < 3; ++k) {
+                const T* t0 = feat + off[k];
+                const T* t1 = t0 + W * FEAT;
+                v[(4 * k + 0) % (CK ? 1 : 12)] = load_feat4(t0);
+                v[(4 * k + 1) % (CK ? 1 : 12)] = load_feat4(t0 + FEAT);
+                v[(4 * k + 2) % (CK ? 1 : 12)] = load_feat4(t1);
+                v[(4 * k + 3) % (CK ? 1 : 12)] = load_feat4(t1 + FEAT);
+            }
         }
         const float* src = X + (lane8 * 4) * AS + q;
         const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
-        const float4 dxw = make_float4(dx.x * wp, dx.y * wp, dx.z * wp, dx.w * wp);
+        const float4 dxw = CK ? dx : make_float4(dx.x * wp, dx.y * wp, dx.z * wp, dx.w * wp);
         // the reductions depend only on the weights and dX: they are issued while the texel loads are still in flight
         float w[12];
 #pragma unroll
@@ -264,8 +272,12 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
             }
         }
         float4 fs = make_float4(0.f, 0.f, 0.f, 0.f);   // this pair's raw bilinear feature, this lane's channels
+        if (CK) {
+            fs = make_float4(v[0].x * wp, v[0].y * wp, v[0].z * wp, v[0].w * wp);
+        } else {
 #pragma unroll
-        for (int e = 0; e < 12; ++e) fma4(fs, w[e], v[e]);
+            for (int e = 0; e < 12; ++e) fma4(fs, w[e], v[e % (CK ? 1 : 12)]);
+        }
         float fdot = (fs.x * dx.x + fs.y * dx.y) + (fs.z * dx.z + fs.w * dx.w);   // <dx, f_p> on this lane's channels
         fdot += __shfl_xor_sync(gmask, fdot, 1);
         fdot += __shfl_xor_sync(gmask, fdot, 2);
@@ -275,7 +287,8 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
             const int k = e >> 2, c = e & 3;
             const float bw = rw[4 + e];
             if (bw != 0.f) {
-                const float dv = fdot * wp * (1.f - rw[17 + k]);
+                // CK: bw already carries the part weight
+                const float dv = CK ? fdot * (1.f - rw[17 + k]) : fdot * wp * (1.f - rw[17 + k]);
                 const int pix = (off[k] >> 5) - k * HW + (c >> 1) * W + (c & 1);
                 atomicAdd(dprob + (size_t)(3 * p + k) * HW + pix, bw * dv);
             }
@@ -309,6 +322,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         const int ray0 = (tile - b * a.tiles_per_sample) * a.rays_per_tile;
         const int rays = min(a.rays_per_tile, n - ray0);
         const int tp = rays * S;
+        const int tb = (a.ck.rec && a.feat) ? a.ck.tile_base[tile] : -1;   // this tile's slice of the pair checkpoint
         if (b != cur_b) {
             if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
             load_part_params(s.part, sc, b, tid, NT);
@@ -332,7 +346,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
 
         // ---- 1. positions, masks, compaction (identical arithmetic to the forward) -----------------
         PHASE(0);   // tile load
-        tile_points<TILE_FINE>(s.t, s.r, s.part, a.g, sc.P, b, ray0, rays, tid);
+        // With the forward's pair checkpoint the active list must be the forward's own (which evaluates the last sample of
+        // a ray too); that sample then flows through with a zero upstream gradient.  Otherwise it is skipped outright.
+        TileGeom geom = a.g;
+        geom.skip_last = tb < 0;
+        tile_points<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
         PHASE(1);   // tile_points
 
@@ -412,7 +430,15 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                     fx[i] = q < cnt ? __ldg(fi + (size_t)s.t.list[c0 + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
-            setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
+            const int pair0 = s.t.pref[c0];
+            if (tb >= 0) {   // records straight from the forward's checkpoint (5 x 128 bit each, coalesced)
+                const float4* src = reinterpret_cast<const float4*>(a.ck.rec + (size_t)(tb + pair0) * REC);
+                float4* dst = reinterpret_cast<float4*>(s.r.rec);
+                const int nq = (s.t.pref[c1] - pair0) * (REC / 4);
+                for (int e = tid; e < nq; e += NT) dst[e] = __ldg(src + e);
+            } else {
+                setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
+            }
             if (a.feat) {
 #pragma unroll
                 for (int i = 0; i < 2; ++i) {
@@ -537,7 +563,8 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             }
             __syncthreads();
             PHASE(11);  // dX
-            scatter_chunk<T>(s.t, s.r.rec, s.X, a, b, c0, c1, tid);
+            if (tb >= 0) scatter_chunk<T, true>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT);
+            else scatter_chunk<T, false>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, nullptr);
             __syncthreads();
             PHASE(12);  // scatter
             c0 = c1;
@@ -550,7 +577,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
 
 extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                      const float* ray_dir, const float* bins, const float* point_saved,
-                                     const float* feat_saved, int n, int Nf,
+                                     const float* feat_saved, const enarf_pair_ckpt_t* pair_ckpt, int n, int Nf,
                                      const float* g_color, const float* g_mask, const float* g_disparity,
                                      const float* g_fine_weights, float* d_feat, float* d_prob,
                                      int64_t d_prob_batch_stride, float* d_w1, float* d_w2, float* d_w3, float* d_b1,
@@ -576,6 +603,12 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     a.g.skip_last = 1;
     a.saved = point_saved;
     a.feat = feat_saved;
+    if (pair_ckpt) {
+        ENARF_REQUIRE(feat_saved && pair_ckpt->rec && pair_ckpt->feat && pair_ckpt->tile_base &&
+                          ((uintptr_t)pair_ckpt->rec & 15) == 0 && ((uintptr_t)pair_ckpt->feat & 15) == 0,
+                      ENARF_ERR_INVALID_ARG, "enarf_render_fine_bwd: the pair checkpoint needs feat_saved and 16-byte aligned buffers");
+        a.ck = *pair_ckpt;
+    }
     a.g_color = g_color;
     a.g_mask = g_mask;
     a.g_disp = g_disparity;

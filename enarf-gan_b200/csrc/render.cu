@@ -36,6 +36,7 @@ struct RenderArgs {
     float* fine_weights;
     float* point_out;
     float* feat_out;    // (B,n,S,32) checkpoint of the gathered features for the backward, or NULL
+    enarf_pair_ckpt_t ck;   // per-pair checkpoint (rec == NULL: none)
     float* q_density;
     float* q_color;
     uint32_t* q_mask;
@@ -86,6 +87,16 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
         if (tid == 0) s.t.pad_[0] = 0;   // chunk counter of this tile
         tile_points<MODE>(s.t, *reinterpret_cast<RecSmem*>(&s.u), s.part, a.g, sc.P, b, ray0, rays, tid);
         const int n_active = s.t.n_active;
+        if (MODE == MODE_FINE && a.ck.rec) {   // hand this tile its slice of the pair checkpoint
+            if (tid == 0) {
+                const int np_tile = s.t.pref[n_active];
+                int base = atomicAdd(a.ck.cursor, np_tile);
+                if ((long long)base + np_tile > a.ck.capacity) base = -1;
+                a.ck.tile_base[tile] = base;
+                s.t.pad_[1] = base;
+            }
+            __syncthreads();
+        }
         if (MODE == MODE_QUERY && a.q_mask)
             for (int i = tid; i < tp; i += NT) a.q_mask[(size_t)b * n + ray0 + i] = __float_as_uint(s.t.pm[i].w);
         float4* out = s.t.pm;
@@ -101,7 +112,9 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 const int a0 = 32 * c;
                 if (a0 >= n_active) break;
                 const int np = min(32, n_active - a0);
-                gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane);
+                const int tb = (MODE == MODE_FINE && a.ck.rec) ? s.t.pad_[1] : -1;
+                gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane,
+                                 tb >= 0 ? a.ck.rec + (size_t)tb * REC : nullptr, tb >= 0 ? a.ck.feat + (size_t)tb * FEAT : nullptr);
                 if (MODE == MODE_FINE && a.feat_out) {   // 8 lanes per point: one 128-B row each
                     float4* fo = reinterpret_cast<float4*>(a.feat_out) + ((size_t)b * n + ray0) * S * (FEAT / 4);
                     for (int q = lane >> 3; q < np; q += 4)
@@ -246,6 +259,13 @@ static int launch_render(RenderArgs& a, const char* who, cudaStream_t stream) {
 
 static int tile_rays(int S) { return max(1, min(MAX_RAYS, TP_MAX / S)); }
 
+// bwd.cu uses the same tile geometry (NT, MAX_RAYS): tile t of the backward is tile t of the forward
+extern "C" int enarf_fine_tiles_per_sample(int n, int Nf) {
+    if (n <= 0 || Nf < 2 || Nf > TP_MAX) return 0;
+    const int r = tile_rays(Nf);
+    return (n + r - 1) / r;
+}
+
 extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                    const float* ray_dir, int n, int Nc, float* weights_out, float* density_out,
                                    void* stream) {
@@ -272,7 +292,7 @@ extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* dept
 extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                      const float* ray_dir, const float* bins, int n, int Nf, float* color,
                                      float* mask, float* disparity, float* fine_weights, float* fine_depth,
-                                     float* point_out, float* feat_out, void* stream) {
+                                     float* point_out, float* feat_out, const enarf_pair_ckpt_t* pair_ckpt, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_fwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && color && mask && disparity && fine_weights && fine_depth,
@@ -298,6 +318,12 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
     a.fine_weights = fine_weights;
     a.point_out = point_out;
     a.feat_out = feat_out;
+    if (pair_ckpt) {
+        ENARF_REQUIRE(pair_ckpt->rec && pair_ckpt->feat && pair_ckpt->tile_base && pair_ckpt->cursor && pair_ckpt->capacity > 0 &&
+                          ((uintptr_t)pair_ckpt->rec & 15) == 0 && ((uintptr_t)pair_ckpt->feat & 15) == 0,
+                      ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: incomplete or misaligned pair checkpoint");
+        a.ck = *pair_ckpt;
+    }
     return launch_render<MODE_FINE>(a, "enarf_render_fine_fwd", (cudaStream_t)stream);
 }
 

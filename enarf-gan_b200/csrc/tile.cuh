@@ -341,9 +341,14 @@ __device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& 
 #endif
 #define XSW 32      // feature slab row stride; 8-float granules are XOR-swizzled by the row (mlp_mma.cuh xs_col)
 
+// Pair checkpoint (include/enarf_b200.h enarf_pair_ckpt_t): ck_rec / ck_feat already point at the tile's first pair,
+// or are NULL.  The checkpointed record is the backward's 20-word layout with the weights premultiplied by the
+// part weight: 0..2 offsets, 3 part | active index << 8, 4..15 weights, 16 1/part weight (0 if the weight is 0),
+// 17..19 sigmoids.
 template <typename T>
 __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, float* X, const float* s_part,
-                                              const enarf_scene_t& sc, int b, int a, int np, int lane) {
+                                              const enarf_scene_t& sc, int b, int a, int np, int lane,
+                                              float* __restrict__ ck_rec = nullptr, float* __restrict__ ck_feat = nullptr) {
     const int H = sc.H, W = sc.W;
     const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
     const int lane8 = lane & 7, grp = lane >> 3;
@@ -369,26 +374,43 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
             float c[3];
             part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
             Bilin bl[3];
-            float wp = 1.f;
+            float sg[3], wp = 1.f;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
-                wp *= sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
+                sg[k] = sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
+                wp *= sg[k];
             }
-            float4* dst = reinterpret_cast<float4*>(rec + r * REC);
-            dst[0] = make_float4(__int_as_float((bl[0].y0 * W + bl[0].x0) * FEAT),
-                                 __int_as_float((H * W + bl[1].y0 * W + bl[1].x0) * FEAT),
-                                 __int_as_float((2 * H * W + bl[2].y0 * W + bl[2].x0) * FEAT), __int_as_float(p));
+            float4 rw[4];
+            rw[0] = make_float4(__int_as_float((bl[0].y0 * W + bl[0].x0) * FEAT),
+                                __int_as_float((H * W + bl[1].y0 * W + bl[1].x0) * FEAT),
+                                __int_as_float((2 * H * W + bl[2].y0 * W + bl[2].x0) * FEAT), __int_as_float(p | (lo << 8)));
 #pragma unroll
             for (int k = 0; k < 3; ++k)
-                dst[1 + k] = make_float4(bl[k].w00 * wp, bl[k].w01 * wp, bl[k].w10 * wp, bl[k].w11 * wp);
+                rw[1 + k] = make_float4(bl[k].w00 * wp, bl[k].w01 * wp, bl[k].w10 * wp, bl[k].w11 * wp);
+            float4* dst = reinterpret_cast<float4*>(rec + r * REC);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) dst[k] = rw[k];
+            if (ck_rec) {
+                float4* g = reinterpret_cast<float4*>(ck_rec + (size_t)target * REC);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) g[k] = rw[k];
+                g[4] = make_float4(wp != 0.f ? __frcp_rn(wp) : 0.f, sg[0], sg[1], sg[2]);
+            }
         }
         __syncwarp();
         // ---- gather: 8 lanes per point, the four groups take points q0+grp, q0+grp+4, ... ---------------
         for (int q = q0 + grp; q < q1; q += 4) {
             float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
             const int r1 = t.pref[a + q + 1] - base;
-            for (int r = t.pref[a + q] - base; r < r1; ++r) gather_pair<T>(f, feat, rec + r * REC, W * FEAT, 1.f);
+            for (int r = t.pref[a + q] - base; r < r1; ++r) {
+                // the pair's own contribution, summed over the point's parts in part order (the same arithmetic whether
+                // or not it is also kept for the backward)
+                float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
+                gather_pair<T>(g, feat, rec + r * REC, W * FEAT, 1.f);
+                if (ck_feat) *reinterpret_cast<float4*>(ck_feat + (size_t)(base + r) * FEAT + 4 * lane8) = g;
+                f.x += g.x; f.y += g.y; f.z += g.z; f.w += g.w;
+            }
             *reinterpret_cast<float4*>(X + q * XSW + ((4 * lane8) ^ (8 * (q & 3)))) = f;
         }
         __syncwarp();

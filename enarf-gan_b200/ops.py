@@ -136,9 +136,42 @@ def density_query(scene, points, want_color=True, want_mask=False):
     return den, col, msk
 
 
-def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False):
+PAIR_CKPT = True              # the forward also keeps per-(point, part) records / features for the backward
+PAIR_CKPT_PER_POINT = 2.0     # capacity in pairs per launched sample point (tiles that do not fit are recomputed)
+PAIR_CKPT_MAX = 48 << 20      # pairs (208 B each)
+
+
+class PairCheckpoint:
+    """Caller-owned buffers of enarf_pair_ckpt_t (include/enarf_b200.h) for one fine pass."""
+
+    def __init__(self, B, n, Nf, device):
+        tiles = lib().enarf_fine_tiles_per_sample(n, Nf)
+        self.capacity = int(max(1, min(PAIR_CKPT_MAX, PAIR_CKPT_PER_POINT * B * n * Nf)))
+        self.rec = torch.empty(self.capacity, 20, device=device)
+        self.feat = torch.empty(self.capacity, FEAT_DIM, device=device)
+        self.tile_base = torch.empty(max(1, B * tiles), device=device, dtype=torch.int32)
+        self.cursor = torch.zeros(1, device=device, dtype=torch.int32)
+        self.c = _abi.PairCkpt(self.rec.data_ptr(), self.feat.data_ptr(), self.tile_base.data_ptr(),
+                               self.cursor.data_ptr(), self.capacity)
+
+    @property
+    def ref(self):
+        return ctypes.byref(self.c)
+
+    def tensors(self):
+        return self.rec, self.feat, self.tile_base, self.cursor
+
+    @classmethod
+    def from_tensors(cls, rec, feat, tile_base, cursor):
+        self = cls.__new__(cls)
+        self.rec, self.feat, self.tile_base, self.cursor, self.capacity = rec, feat, tile_base, cursor, rec.shape[0]
+        self.c = _abi.PairCkpt(rec.data_ptr(), feat.data_ptr(), tile_base.data_ptr(), cursor.data_ptr(), self.capacity)
+        return self
+
+
+def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False, want_pairs=False):
     """-> color, mask, disp, fine_weights, fine_depth [, points (B,n,Nf,4)] [, feat (B,n,Nf,32) checkpoint: only
-    the rows of samples inside a part are written]."""
+    the rows of samples inside a part are written] [, PairCheckpoint]."""
     B, n, Nf = bins.shape
     dev = bins.device
     color = torch.empty(B, 3, n, device=dev)
@@ -148,14 +181,17 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     fd = torch.empty(B, n, Nf, device=dev)
     pts = torch.empty(B, n, Nf, 4, device=dev) if want_points else None
     feat = torch.empty(B, n, Nf, FEAT_DIM, device=dev) if want_feat else None
+    pairs = PairCheckpoint(B, n, Nf, dev) if want_pairs else None
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
                                       ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True),
-                                      ptr(feat, allow_none=True), stream_ptr()))
+                                      ptr(feat, allow_none=True), pairs.ref if pairs else None, stream_ptr()))
     out = (color, mask, disp, fw, fd)
     if want_points:
         out += (pts,)
     if want_feat:
         out += (feat,)
+    if want_pairs:
+        out += (pairs,)
     return out
 
 
@@ -166,9 +202,17 @@ class RenderFine(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES)
+        pairs_on = SAVE_FEATURES and PAIR_CKPT
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
+                               want_pairs=pairs_on)
         ctx.scene = scene
-        ctx.save_for_backward(dmin, dmax, direction, bins, out[5], *(out[6:]))
+        saved = [dmin, dmax, direction, bins, out[5]]
+        if SAVE_FEATURES:
+            saved.append(out[6])
+        if pairs_on:
+            saved.extend(out[7].tensors())
+        ctx.has_feat, ctx.has_pairs = SAVE_FEATURES, pairs_on
+        ctx.save_for_backward(*saved)
         out = out[:6]
         ctx.tp_shape = tri_plane.shape
         ctx.mark_non_differentiable(out[4], out[5])
@@ -177,8 +221,9 @@ class RenderFine(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
         scene = ctx.scene
-        dmin, dmax, direction, bins, pts, *feat = ctx.saved_tensors
-        feat = feat[0] if feat else None
+        dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
+        feat = rest.pop(0) if ctx.has_feat else None
+        pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
         B, n, Nf = bins.shape
         dev = bins.device
         c = lambda g: None if g is None else g.contiguous().float()
@@ -194,7 +239,8 @@ class RenderFine(torch.autograd.Function):
         db = [torch.zeros_like(b) for b in scene.b]
         g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
         check(lib().enarf_render_fine_bwd(
-            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True), n, Nf,
+            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True),
+            pairs.ref if pairs else None, n, Nf,
             ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
             ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
             ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))

@@ -100,6 +100,21 @@ int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, con
                       const float* jitter, uint64_t seed, int64_t ray_id_offset, float* bins_out,
                       int32_t* idx_out, void* stream);
 
+/* Optional per-(sample point, part) checkpoint written by the fine forward and consumed by the fine backward, so
+ * that the backward neither rebuilds its pair records (canonical coordinates, bilinear footprints, 12 probability
+ * texels, sigmoids) nor re-reads the 12 feature texels of every pair.  The caller owns all buffers and zeroes
+ * `cursor` before the forward; tiles that do not fit `capacity` are marked -1 in tile_base and the backward
+ * recomputes them.  tile_base has B * enarf_fine_tiles_per_sample(n, Nf) entries. */
+typedef struct {
+    float* rec;          /* (capacity, 20): texel offsets, part | active index << 8, 12 weights x part weight,
+                            1 / part weight, 3 sigmoids */
+    float* feat;         /* (capacity, 32): part-weighted bilinear feature of the pair; 16-byte aligned */
+    int32_t* tile_base;  /* first pair of every tile, -1 if the tile was not checkpointed */
+    int32_t* cursor;     /* one int: pairs handed out so far */
+    int64_t capacity;    /* pairs */
+} enarf_pair_ckpt_t;
+int enarf_fine_tiles_per_sample(int n, int Nf);
+
 /* Fine pass forward, fused gather -> decoder -> compositing (rendering.py:198-200,283-335).
  * bins (B,n,Nf) sorted.  Outputs: color (B,3,n), mask (B,n), disparity (B,n),
  * fine_weights (B,n,Nf-1), fine_depth (B,n,Nf); point_out (B,n,Nf,4) = per-sample (r,g,b,sigma), optional
@@ -110,16 +125,16 @@ int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, con
 int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, int n, int Nf, float* color, float* mask,
                           float* disparity, float* fine_weights, float* fine_depth, float* point_out,
-                          float* feat_out, void* stream);
+                          float* feat_out, const enarf_pair_ckpt_t* pair_ckpt /* NULL = none */, void* stream);
 
 /* Fine pass backward.  point_saved (B,n,Nf,4) is the forward's point_out; feat_saved (B,n,Nf,32) is the forward's
- * feat_out or NULL (the features are then gathered again).  Upstream gradients (any may be NULL = zero):
+ * feat_out or NULL (the features are then gathered again); pair_ckpt requires feat_saved.  Upstream gradients (any may be NULL = zero):
  * g_color (B,3,n), g_mask (B,n), g_disparity (B,n), g_fine_weights (B,n,Nf-1).  Gradient buffers (caller
  * zero-initialises; results are ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as
  * scene->prob_planes, d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4). */
 int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, const float* point_saved, const float* feat_saved,
-                          int n, int Nf, const float* g_color, const float* g_mask, const float* g_disparity,
+                          const enarf_pair_ckpt_t* pair_ckpt /* the forward's, or NULL */, int n, int Nf, const float* g_color, const float* g_mask, const float* g_disparity,
                           const float* g_fine_weights, float* d_feat, float* d_prob, int64_t d_prob_batch_stride,
                           float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, void* stream);
 

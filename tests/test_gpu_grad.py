@@ -67,12 +67,17 @@ def test_fine_pass_gradients(name, dtype, tol, btol):
         assert rel(b.grad, br.grad) < btol, f"db{i + 1}"
 
 
-@pytest.mark.parametrize("save_features", [True, False])
-def test_backward_with_missing_upstream_grads(save_features, monkeypatch):
-    """Only colour feeds the loss: the NULL-gradient paths of the ABI; with the forward's feature checkpoint
-    (feat_saved) and without it (the backward gathers again)."""
+@pytest.mark.parametrize("save_features,pair_ckpt,capacity", [(True, True, None), (True, True, 3000), (True, False, None),
+                                                              (False, False, None)])
+def test_backward_with_missing_upstream_grads(save_features, pair_ckpt, capacity, monkeypatch):
+    """Only colour feeds the loss: the NULL-gradient paths of the ABI; with the forward's per-pair and per-point
+    checkpoints, with a pair checkpoint too small for most tiles (they fall back to recomputing their records),
+    with the per-point feature checkpoint only, and with none (the backward gathers again)."""
     from enarf_gan_b200 import ops
     monkeypatch.setattr(ops, "SAVE_FEATURES", save_features)
+    monkeypatch.setattr(ops, "PAIR_CKPT", pair_ckpt)
+    if capacity is not None:
+        monkeypatch.setattr(ops, "PAIR_CKPT_MAX", capacity)
     g, cfg, inp, tp, layers, z_rend = G.load("b2_s24")
     sc = G.scene(cfg, inp, tp, layers, z_rend, torch.float32)
     B, Nc, Nf = cfg["B"], cfg["Nc"], cfg["Nf"]
