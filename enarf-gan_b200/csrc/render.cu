@@ -90,8 +90,12 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
         if (MODE == MODE_FINE && a.ck.rec) {   // hand this tile its slice of the pair checkpoint
             if (tid == 0) {
                 const int np_tile = s.t.pref[n_active];
-                int base = atomicAdd(a.ck.cursor, np_tile);
-                if ((long long)base + np_tile > a.ck.capacity) base = -1;
+                // once the checkpoint is full the cursor is left alone, so it cannot wrap however many tiles follow
+                int base = -1;
+                if (*reinterpret_cast<volatile int*>(a.ck.cursor) <= a.ck.capacity) {
+                    base = atomicAdd(a.ck.cursor, np_tile);
+                    if ((long long)base + np_tile > a.ck.capacity) base = -1;
+                }
                 a.ck.tile_base[tile] = base;
                 s.t.pad_[1] = base;
             }

@@ -57,6 +57,31 @@ __global__ void __launch_bounds__(WARPS * 32) fine_sample_kernel(
             val[sidx] = v;
         }
         __syncwarp();
+        if (Nf2 == 64) {
+            // bitonic sort of 64 values in registers: element i lives in lane i & 31, register i >> 5; partners at
+            // distance < 32 are exchanged by shuffle, distance 32 is the lane's own second register
+            float v0 = val[lane], v1 = val[lane + 32];
+#pragma unroll
+            for (int k = 2; k <= 64; k <<= 1) {
+#pragma unroll
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    if (j == 32) {
+                        const float lo = fminf(v0, v1), hi = fmaxf(v0, v1);   // k == 64: ascending everywhere
+                        v0 = lo;
+                        v1 = hi;
+                    } else {
+                        const float p0 = __shfl_xor_sync(0xffffffffu, v0, j), p1 = __shfl_xor_sync(0xffffffffu, v1, j);
+                        const bool lower = (lane & j) == 0;            // this lane holds the lower index of the pair
+                        const bool up0 = (lane & k) == 0, up1 = ((lane + 32) & k) == 0;
+                        v0 = (lower == up0) ? fminf(v0, p0) : fmaxf(v0, p0);
+                        v1 = (lower == up1) ? fminf(v1, p1) : fmaxf(v1, p1);
+                    }
+                }
+            }
+            val[lane] = v0;
+            val[lane + 32] = v1;
+            __syncwarp();
+        } else
         for (int k = 2; k <= Nf2; k <<= 1) {          // bitonic sort, ascending
             for (int j = k >> 1; j > 0; j >>= 1) {
                 for (int i = lane; i < Nf2; i += 32) {
