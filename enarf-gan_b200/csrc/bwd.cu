@@ -413,23 +413,25 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         PHASE(2);   // composite backward
 
         // ---- 3. per chunk: records -> gather -> decoder forward -> decoder backward -> scatter -------
+        // Features checkpointed by the forward: 8 lanes per point, one 128-B row each.  A chunk's rows are loaded into
+        // registers one chunk ahead (before the previous chunk's scatter) and stored to shared memory at its start.
+        static_assert(CH == 2 * (NT / 8), "two checkpoint rows per 8-lane group");
+        float4 fx[2];
+        const int l8 = tid & 7;
+        const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
+        auto load_rows = [&](int first, int count) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int q = (tid >> 3) + i * (NT / 8);
+                fx[i] = q < count ? __ldg(fi + (size_t)s.t.list[first + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        int c1 = n_active > 0 ? chunk_end(s.t, 0) : 0;
+        if (a.feat && n_active > 0) load_rows(0, c1);
         for (int c0 = 0; c0 < n_active;) {
-            const int c1 = chunk_end(s.t, c0), cnt = c1 - c0;
+            const int cnt = c1 - c0;
             const int cend = (cnt + 31) & ~31;
             const bool tile_on = 32 * m.pb < cnt;   // this warp's 32 points intersect the chunk
-            // features checkpointed by the forward: 8 lanes per point, one 128-B row each.  The loads are issued
-            // before the pair set-up (itself bound by the latency of its probability texels) and stored after it.
-            static_assert(CH == 2 * (NT / 8), "two checkpoint rows per 8-lane group");
-            float4 fx[2];
-            const int l8 = tid & 7;
-            if (a.feat) {
-                const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    const int q = (tid >> 3) + i * (NT / 8);
-                    fx[i] = q < cnt ? __ldg(fi + (size_t)s.t.list[c0 + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
-                }
-            }
             const int pair0 = s.t.pref[c0];
             if (tb >= 0) {   // records straight from the forward's checkpoint (5 x 128 bit each, coalesced)
                 const float4* src = reinterpret_cast<const float4*>(a.ck.rec + (size_t)(tb + pair0) * REC);
@@ -563,11 +565,14 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             }
             __syncthreads();
             PHASE(11);  // dX
+            const int c1n = c1 < n_active ? chunk_end(s.t, c1) : c1;
+            if (a.feat && c1 < n_active) load_rows(c1, c1n - c1);   // next chunk's rows, in flight during the scatter
             if (tb >= 0) scatter_chunk<T, true>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT);
             else scatter_chunk<T, false>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, nullptr);
             __syncthreads();
             PHASE(12);  // scatter
             c0 = c1;
+            c1 = c1n;
         }
     }
     if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
