@@ -437,7 +437,12 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 const float4* src = reinterpret_cast<const float4*>(a.ck.rec + (size_t)(tb + pair0) * REC);
                 float4* dst = reinterpret_cast<float4*>(s.r.rec);
                 const int nq = (s.t.pref[c1] - pair0) * (REC / 4);
-                for (int e = tid; e < nq; e += NT) dst[e] = __ldg(src + e);
+                // asynchronous copy: the records are only needed by the scatter at the end of the chunk
+                for (int e = tid; e < nq; e += NT)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + e)),
+                                 "l"(src + e)
+                                 : "memory");
+                asm volatile("cp.async.commit_group;" ::: "memory");
             } else {
                 setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             }
@@ -563,6 +568,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                     d0[AS + 8] = acc[mt][0][3];
                 }
             }
+            if (tb >= 0) asm volatile("cp.async.wait_group 0;" ::: "memory");   // this chunk's records have landed
             __syncthreads();
             PHASE(11);  // dX
             const int c1n = c1 < n_active ? chunk_end(s.t, c1) : c1;
