@@ -122,8 +122,8 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 if (MODE == MODE_FINE && a.feat_out) {   // 8 lanes per point: one 128-B row each
                     float4* fo = reinterpret_cast<float4*>(a.feat_out) + ((size_t)b * n + ray0) * S * (FEAT / 4);
                     for (int q = lane >> 3; q < np; q += 4)
-                        fo[(size_t)s.t.list[a0 + q] * (FEAT / 4) + (lane & 7)] =
-                            *reinterpret_cast<const float4*>(my.X + q * XSW + xs_col(q, 4 * (lane & 7)));
+                        __stcs(fo + (size_t)s.t.list[a0 + q] * (FEAT / 4) + (lane & 7),
+                               *reinterpret_cast<const float4*>(my.X + q * XSW + xs_col(q, 4 * (lane & 7))));
                 }
                 float o3[2][4];
                 decode32_mma(my.X, s.dec, lane, o3);

@@ -392,10 +392,11 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
 #pragma unroll
             for (int k = 0; k < 4; ++k) dst[k] = rw[k];
             if (ck_rec) {
+                // streaming stores: the checkpoint is written once and must not push the planes out of L2
                 float4* g = reinterpret_cast<float4*>(ck_rec + (size_t)target * REC);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) g[k] = rw[k];
-                g[4] = make_float4(wp != 0.f ? __frcp_rn(wp) : 0.f, sg[0], sg[1], sg[2]);
+                for (int k = 0; k < 4; ++k) __stcs(g + k, rw[k]);
+                __stcs(g + 4, make_float4(wp != 0.f ? __frcp_rn(wp) : 0.f, sg[0], sg[1], sg[2]));
             }
         }
         __syncwarp();
@@ -408,7 +409,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
                 // or not it is also kept for the backward)
                 float4 g = make_float4(0.f, 0.f, 0.f, 0.f);
                 gather_pair<T>(g, feat, rec + r * REC, W * FEAT, 1.f);
-                if (ck_feat) *reinterpret_cast<float4*>(ck_feat + (size_t)(base + r) * FEAT + 4 * lane8) = g;
+                if (ck_feat) __stcs(reinterpret_cast<float4*>(ck_feat + (size_t)(base + r) * FEAT + 4 * lane8), g);
                 f.x += g.x; f.y += g.y; f.z += g.z; f.w += g.w;
             }
             *reinterpret_cast<float4*>(X + q * XSW + ((4 * lane8) ^ (8 * (q & 3)))) = f;
