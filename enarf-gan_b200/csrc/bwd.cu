@@ -426,8 +426,26 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 fx[i] = q < count ? __ldg(fi + (size_t)s.t.list[first + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
             }
         };
+        auto store_rows = [&](int count) {   // fx -> X[channel][point], columns up to the next multiple of 32 zero-filled
+            const int cend_ = (count + 31) & ~31;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int q = (tid >> 3) + i * (NT / 8);
+                if (q < cend_) {
+                    float* dst = s.X + (l8 * 4) * AS + q;
+                    dst[0] = fx[i].x;
+                    dst[AS] = fx[i].y;
+                    dst[2 * AS] = fx[i].z;
+                    dst[3 * AS] = fx[i].w;
+                }
+            }
+        };
         int c1 = n_active > 0 ? chunk_end(s.t, 0) : 0;
-        if (a.feat && n_active > 0) load_rows(0, c1);
+        if (a.feat && n_active > 0) {
+            load_rows(0, c1);
+            store_rows(c1);
+        }
+        __syncthreads();
         for (int c0 = 0; c0 < n_active;) {
             const int cnt = c1 - c0;
             const int cend = (cnt + 31) & ~31;
@@ -446,23 +464,12 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             } else {
                 setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             }
-            if (a.feat) {
-#pragma unroll
-                for (int i = 0; i < 2; ++i) {
-                    const int q = (tid >> 3) + i * (NT / 8);
-                    if (q < cend) {
-                        float* dst = s.X + (l8 * 4) * AS + q;
-                        dst[0] = fx[i].x;
-                        dst[AS] = fx[i].y;
-                        dst[2 * AS] = fx[i].z;
-                        dst[3 * AS] = fx[i].w;
-                    }
-                }
-            } else {
+            if (!a.feat) {   // no feature checkpoint: gather again (needs the records)
                 __syncthreads();
                 gather_chunk<T, true>(s.t, s.r.rec, s.X, sc, b, c0, c1, tid);
+                __syncthreads();
             }
-            __syncthreads();
+            // with the checkpoint, X of this chunk was stored during the previous chunk's scatter (or before the loop)
             PHASE(3);   // records + X load
             if (tile_on) decoder_layer<FEAT>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
@@ -553,15 +560,14 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             PHASE(9);   // G1
             // dW1 += G1^T X: warp tile rows (o) 16 wr.., cols (c) 8 TN1 wc..
             wgrad_mma<TN1>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
-            __syncthreads();
-            PHASE(10);  // dW1
-            if (tile_on) {   // dX = G1 W1, in place over X: warp tile points 32 pb.., channels 8 ob..
+            // no barrier: dX goes to the rows of A2 (G2 is dead after the G1 phase), so X and G1 are only read here
+            if (tile_on) {   // dX = G1 W1 -> A2 rows 0..31: warp tile points 32 pb.., channels 8 ob..
                 float acc[2][1][4];
                 gemm_pts_mma<HID, 1, true>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
                 const int col = 8 * m.ob + 2 * m.t;
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {
-                    float* d0 = s.X + col * AS + 32 * m.pb + 16 * mt + m.g;
+                    float* d0 = s.A2 + col * AS + 32 * m.pb + 16 * mt + m.g;
                     d0[0] = acc[mt][0][0];
                     d0[AS] = acc[mt][0][1];
                     d0[8] = acc[mt][0][2];
@@ -573,8 +579,9 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             PHASE(11);  // dX
             const int c1n = c1 < n_active ? chunk_end(s.t, c1) : c1;
             if (a.feat && c1 < n_active) load_rows(c1, c1n - c1);   // next chunk's rows, in flight during the scatter
-            if (tb >= 0) scatter_chunk<T, true>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT);
-            else scatter_chunk<T, false>(s.t, s.r.rec, s.X, a, b, c0, c1, tid, nullptr);
+            if (tb >= 0) scatter_chunk<T, true>(s.t, s.r.rec, s.A2, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT);
+            else scatter_chunk<T, false>(s.t, s.r.rec, s.A2, a, b, c0, c1, tid, nullptr);
+            if (a.feat && c1 < n_active) store_rows(c1n - c1);   // X is free since the dW1 / dX phase
             __syncthreads();
             PHASE(12);  // scatter
             c0 = c1;
