@@ -5,40 +5,51 @@
 #include "common.cuh"
 
 // ---- NCHW feature channels <-> channels-last (B,3,H,W,32) ---------------------------------------
-// One CTA transposes a 32-channel x 32-texel tile through shared memory: 128-B coalesced reads along x,
-// 128-B coalesced writes along the channel axis.
+// One CTA transposes a 32-channel x TPX-texel tile through shared memory: each warp reads 1 KB runs along x of one
+// channel row (the rows are H*W floats apart, so short runs would touch a new DRAM page every 128 B), and writes
+// 128-B texels along the channel axis; the 257-float row stride keeps both sides bank-conflict free.
+#define TPX 256
 template <typename T>
 __global__ void __launch_bounds__(256) repack_kernel(const float* __restrict__ src, int C_total, int HW,
                                                      T* __restrict__ dst) {
-    __shared__ float tile[32][33];
+    __shared__ float tile[32][TPX + 1];
     const int bk = blockIdx.y;  // b*3 + k
     const int b = bk / 3, k = bk - b * 3;
-    const int x0 = blockIdx.x * 32;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-    const float* s = src + ((size_t)b * C_total + k * FEAT) * HW;
-    for (int c = ty; c < 32; c += 8) tile[c][tx] = (x0 + tx < HW) ? s[(size_t)c * HW + x0 + tx] : 0.f;
+    const int x0 = blockIdx.x * TPX;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const float* s = src + ((size_t)b * C_total + k * FEAT) * HW + x0;
+    for (int c = warp; c < 32; c += 8)
+#pragma unroll
+        for (int j = 0; j < TPX / 32; ++j) {
+            const int x = 32 * j + lane;
+            tile[c][x] = (x0 + x < HW) ? __ldg(s + (size_t)c * HW + x) : 0.f;
+        }
     __syncthreads();
     T* d = dst + ((size_t)bk * HW + x0) * FEAT;
-    for (int p = ty; p < 32; p += 8)
-        if (x0 + p < HW) d[(size_t)p * FEAT + tx] = (T)tile[tx][p];
+    for (int p = warp; p < TPX; p += 8)
+        if (x0 + p < HW) d[(size_t)p * FEAT + lane] = (T)tile[lane][p];
 }
 
 template <bool ACC>
 __global__ void __launch_bounds__(256) unpack_grad_kernel(const float* __restrict__ d_feat, int C_total, int HW,
                                                           float* __restrict__ d_nchw) {
-    __shared__ float tile[32][33];
+    __shared__ float tile[32][TPX + 1];
     const int bk = blockIdx.y;
     const int b = bk / 3, k = bk - b * 3;
-    const int x0 = blockIdx.x * 32;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int x0 = blockIdx.x * TPX;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const float* s = d_feat + ((size_t)bk * HW + x0) * FEAT;
-    for (int p = ty; p < 32; p += 8) tile[p][tx] = (x0 + p < HW) ? s[(size_t)p * FEAT + tx] : 0.f;
+    for (int p = warp; p < TPX; p += 8) tile[lane][p] = (x0 + p < HW) ? __ldg(s + (size_t)p * FEAT + lane) : 0.f;
     __syncthreads();
-    float* d = d_nchw + ((size_t)b * C_total + k * FEAT) * HW;
-    for (int c = ty; c < 32; c += 8)
-        if (x0 + tx < HW) {
-            float* o = d + (size_t)c * HW + x0 + tx;
-            *o = ACC ? *o + tile[tx][c] : tile[tx][c];
+    float* d = d_nchw + ((size_t)b * C_total + k * FEAT) * HW + x0;
+    for (int c = warp; c < 32; c += 8)
+#pragma unroll
+        for (int j = 0; j < TPX / 32; ++j) {
+            const int x = 32 * j + lane;
+            if (x0 + x < HW) {
+                float* o = d + (size_t)c * HW + x;
+                *o = ACC ? *o + tile[c][x] : tile[c][x];
+            }
         }
 }
 
@@ -48,7 +59,7 @@ extern "C" int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_tot
                   "enarf_repack_planes: bad arguments (C_total=%d)", C_total);
     ENARF_REQUIRE(3 * B <= 65535, ENARF_ERR_UNSUPPORTED, "enarf_repack_planes: batch %d too large", B);
     const int HW = H * W;
-    dim3 grid((HW + 31) / 32, 3 * B);
+    dim3 grid((HW + TPX - 1) / TPX, 3 * B);
     if (out_dtype == ENARF_DTYPE_F32)
         repack_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(tri_plane_nchw, C_total, HW, (float*)feat_out);
     else if (out_dtype == ENARF_DTYPE_BF16)
@@ -66,7 +77,7 @@ extern "C" int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total,
                   "enarf_unpack_plane_grads: bad arguments");
     ENARF_REQUIRE(3 * B <= 65535, ENARF_ERR_UNSUPPORTED, "enarf_unpack_plane_grads: batch %d too large", B);
     const int HW = H * W;
-    dim3 grid((HW + 31) / 32, 3 * B);
+    dim3 grid((HW + TPX - 1) / TPX, 3 * B);
     if (accumulate)
         unpack_grad_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_feat, C_total, HW, d_tri_plane_nchw);
     else
