@@ -70,8 +70,9 @@ __device__ __forceinline__ void mma3(float (&main)[4], float (&small)[4], const 
 // only influences its own outputs).  Returns the head's pre-activation outputs as accumulator fragments:
 // o3[mt][0] = (point 16mt+g,   channel 2t)   o3[mt][1] = (point 16mt+g,   channel 2t+1)
 // o3[mt][2] = (point 16mt+g+8, channel 2t)   o3[mt][3] = (point 16mt+g+8, channel 2t+1);  channels >= 4 are padding.
-__device__ __forceinline__ void decode32_mma(const float* __restrict__ X, const DecoderMma& d, int lane,
-                                             float (&o3)[2][4]) {
+// A1: at least 32 * A1S floats of the warp's own shared memory, may alias X.
+#define A1S 64
+__device__ __forceinline__ void decode32_mma(const float* X, float* A1, const DecoderMma& d, int lane, float (&o3)[2][4]) {
     const int g = lane >> 2, t = lane & 3;
     float acc1[2][8][4];
 #pragma unroll
@@ -121,36 +122,65 @@ __device__ __forceinline__ void decode32_mma(const float* __restrict__ X, const 
         }
     }
 
-    // ---- layer 2 (64 -> 64) one n-tile at a time, each finished n-tile feeding layer 3 (64 -> 4) as a k-block --
+    // ---- layer-1 activations -> the warp's slab (X and the record slab behind it are dead by now), as
+    // [32 points][64 channels] with the same granule swizzle: frees the 64 accumulator registers, so that layer 2
+    // can keep all 8 n-tiles in flight (16 independent mma chains, like layer 1) instead of one n-tile at a time
+    __syncwarp();   // every lane has read its X fragments
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt) {
+        const int col = xs_col(g, 8 * nt + 2 * t);
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            *reinterpret_cast<float2*>(A1 + (16 * mt + g) * A1S + col) = make_float2(acc1[mt][nt][0], acc1[mt][nt][1]);
+            *reinterpret_cast<float2*>(A1 + (16 * mt + g + 8) * A1S + col) = make_float2(acc1[mt][nt][2], acc1[mt][nt][3]);
+        }
+    }
+    __syncwarp();
+
+    // ---- layer 2: 64 -> 64 -------------------------------------------------------------------------------
+    float acc2[2][8][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) acc2[mt][nt][i] = 0.f;
+#pragma unroll 1
+    for (int j = 0; j < HID / 8; ++j) {
+        uint32_t ah[2][4], al[2][4];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+            const int col = xs_col(g, 8 * j + 2 * t);
+            const float2 v0 = *reinterpret_cast<const float2*>(A1 + (16 * mt + g) * A1S + col);
+            const float2 v1 = *reinterpret_cast<const float2*>(A1 + (16 * mt + g + 8) * A1S + col);
+            split_tf32(v0.x, ah[mt][0], al[mt][0]);
+            split_tf32(v1.x, ah[mt][1], al[mt][1]);
+            split_tf32(v0.y, ah[mt][2], al[mt][2]);
+            split_tf32(v1.y, ah[mt][3], al[mt][3]);
+        }
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const float2 w = *reinterpret_cast<const float2*>(d.w2 + (8 * nt + g) * W2M + 8 * j + 2 * t);
+            uint32_t bh0, bl0, bh1, bl1;
+            split_tf32(w.x, bh0, bl0);
+            split_tf32(w.y, bh1, bl1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], al[mt], bh0, bh1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], ah[mt], bl0, bl1);
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], ah[mt], bh0, bh1);
+        }
+    }
+
+    // ---- layer 3 (64 -> 4): the finished n-tiles of layer 2 are its k-blocks, straight from the accumulators ---
     float m3[2][4], s3[2][4];
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
         for (int i = 0; i < 4; ++i) m3[mt][i] = s3[mt][i] = 0.f;
-#pragma unroll 1
+#pragma unroll
     for (int nt = 0; nt < 8; ++nt) {
-        float m2[2][4], s2[2][4];
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) m2[mt][i] = s2[mt][i] = 0.f;
-        const float* wrow = d.w2 + (8 * nt + g) * W2M + 2 * t;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float2 w = *reinterpret_cast<const float2*>(wrow + 8 * j);
-            uint32_t bh0, bl0, bh1, bl1;
-            split_tf32(w.x, bh0, bl0);
-            split_tf32(w.y, bh1, bl1);
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt) {
-                uint32_t ah[4], al[4];
-                split_tf32(acc1[mt][j][0], ah[0], al[0]);
-                split_tf32(acc1[mt][j][2], ah[1], al[1]);
-                split_tf32(acc1[mt][j][1], ah[2], al[2]);
-                split_tf32(acc1[mt][j][3], ah[3], al[3]);
-                mma3(m2[mt], s2[mt], ah, al, bh0, bh1, bl0, bl1);
-            }
-        }
         const float2 b = *reinterpret_cast<const float2*>(d.b2 + 8 * nt + 2 * t);
         const float2 w3 = *reinterpret_cast<const float2*>(d.w3 + g * W2M + 8 * nt + 2 * t);
         uint32_t bh0, bl0, bh1, bl1;
@@ -159,10 +189,10 @@ __device__ __forceinline__ void decode32_mma(const float* __restrict__ X, const 
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
             uint32_t ah[4], al[4];
-            split_tf32(lrelu_s2(m2[mt][0] + s2[mt][0] + b.x), ah[0], al[0]);
-            split_tf32(lrelu_s2(m2[mt][2] + s2[mt][2] + b.x), ah[1], al[1]);
-            split_tf32(lrelu_s2(m2[mt][1] + s2[mt][1] + b.y), ah[2], al[2]);
-            split_tf32(lrelu_s2(m2[mt][3] + s2[mt][3] + b.y), ah[3], al[3]);
+            split_tf32(lrelu_s2(acc2[mt][nt][0] + b.x), ah[0], al[0]);
+            split_tf32(lrelu_s2(acc2[mt][nt][2] + b.x), ah[1], al[1]);
+            split_tf32(lrelu_s2(acc2[mt][nt][1] + b.y), ah[2], al[2]);
+            split_tf32(lrelu_s2(acc2[mt][nt][3] + b.y), ah[3], al[3]);
             mma3(m3[mt], s3[mt], ah, al, bh0, bh1, bl0, bl1);
         }
     }

@@ -17,6 +17,20 @@
 #define NT 256
 #define MAX_RAYS 16
 #define RECW 52
+#ifdef ENARF_PHASE_TIMING   // development build: per-warp clock64() sums (lane 0 of every warp), scripts/fwd_phases.py
+struct FwdTimer {
+    long long t;
+    unsigned long long acc[8];
+};
+#define FWD_TIMER_PARAM , FwdTimer& ftm
+#define FWD_TIMER_ARG , ftm
+#define FWD_PHASE(i) do { if ((threadIdx.x & 31) == 0) { const long long now_ = clock64(); ftm.acc[i] += (unsigned long long)(now_ - ftm.t); ftm.t = now_; } } while (0)
+static __device__ unsigned long long g_fwd_phase[8];
+#else
+#define FWD_TIMER_PARAM
+#define FWD_TIMER_ARG
+#define FWD_PHASE(i)
+#endif
 #include "tile.cuh"
 #include "mlp_mma.cuh"
 
@@ -42,6 +56,7 @@ struct RenderArgs {
     uint32_t* q_mask;
 };
 
+static_assert((32 * XSW + RECW * REC) >= 32 * 64, "the slab holds the 32 x 64 layer-1 activations");
 struct __align__(16) WarpSlab {
     float X[32 * XSW];        // features of the warp's 32 points, [point][channel]
     float rec[RECW * REC];    // pair records of the current sub-batch
@@ -68,9 +83,14 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
     const int S = a.g.S, n = a.g.n;
     const int total_tiles = sc.B * a.tiles_per_sample;
     int cur_b = -1;
+#ifdef ENARF_PHASE_TIMING
+    FwdTimer ftm = {};
+    ftm.t = clock64();
+#endif
 
     for (;;) {
         __syncthreads();  // everyone is done with the previous tile (and with s.t.tile)
+        FWD_PHASE(5);   // outputs / compositing of the previous tile + wait for the others
         if (tid == 0) s.t.tile = atomicAdd(a.tile_counter, 1);
         __syncthreads();
         const int tile = s.t.tile;
@@ -105,6 +125,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             for (int i = tid; i < tp; i += NT) a.q_mask[(size_t)b * n + ray0 + i] = __float_as_uint(s.t.pm[i].w);
         float4* out = s.t.pm;
 
+        FWD_PHASE(0);   // tile prologue: rays, phase 0/1, compaction, prefix
         // ---- chunks of 32 active points, one warp each, no CTA barrier ---------------------------------
         {
             WarpSlab& my = s.u.slab[warp];
@@ -118,7 +139,8 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 const int np = min(32, n_active - a0);
                 const int tb = (MODE == MODE_FINE && a.ck.rec) ? s.t.pad_[1] : -1;
                 gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane,
-                                 tb >= 0 ? a.ck.rec + (size_t)tb * REC : nullptr, tb >= 0 ? a.ck.feat + (size_t)tb * FEAT : nullptr);
+                                 tb >= 0 ? a.ck.rec + (size_t)tb * REC : nullptr, tb >= 0 ? a.ck.feat + (size_t)tb * FEAT : nullptr
+                                 FWD_TIMER_ARG);
                 if (MODE == MODE_FINE && a.feat_out) {   // 8 lanes per point: one 128-B row each
                     float4* fo = reinterpret_cast<float4*>(a.feat_out) + ((size_t)b * n + ray0) * S * (FEAT / 4);
                     for (int q = lane >> 3; q < np; q += 4)
@@ -126,7 +148,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                                *reinterpret_cast<const float4*>(my.X + q * XSW + xs_col(q, 4 * (lane & 7))));
                 }
                 float o3[2][4];
-                decode32_mma(my.X, s.dec, lane, o3);
+                decode32_mma(my.X, my.X, s.dec, lane, o3);   // layer-1 activations overwrite the slab (X + records)
                 __syncwarp();   // every lane is done reading X before the next chunk's gather overwrites it
                 // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl. the
                 // last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318).
@@ -145,9 +167,12 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                             }
                         }
                 }
+                FWD_PHASE(3);   // checkpoint row store + decoder + head
             }
         }
+        FWD_PHASE(6);   // failed chunk claim
         __syncthreads();
+        FWD_PHASE(4);   // idle at the end of the tile's chunk phase
 
         // ---- outputs ---------------------------------------------------------------------------------
         if (MODE == MODE_QUERY) {
@@ -232,7 +257,22 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             }
         }
     }
+#ifdef ENARF_PHASE_TIMING
+    if ((threadIdx.x & 31) == 0)
+        for (int i_ = 0; i_ < 8; ++i_) atomicAdd(&g_fwd_phase[i_], ftm.acc[i_]);
+#endif
 }
+
+#ifdef ENARF_PHASE_TIMING
+extern "C" int enarf_debug_fwd_phases(unsigned long long* host_out, int reset) {
+    cudaMemcpyFromSymbol(host_out, g_fwd_phase, sizeof(g_fwd_phase));
+    if (reset) {
+        unsigned long long z[8] = {};
+        cudaMemcpyToSymbol(g_fwd_phase, z, sizeof(z));
+    }
+    return 0;
+}
+#endif
 
 // ---- host side -----------------------------------------------------------------------------------
 template <int MODE>

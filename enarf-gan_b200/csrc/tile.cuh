@@ -341,6 +341,10 @@ __device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& 
 #endif
 #define XSW 32      // feature slab row stride; 8-float granules are XOR-swizzled by the row (mlp_mma.cuh xs_col)
 
+#ifndef FWD_PHASE   // render.cu's development-build phase timer
+#define FWD_PHASE(i)
+#define FWD_TIMER_PARAM
+#endif
 // Pair checkpoint (include/enarf_b200.h enarf_pair_ckpt_t): ck_rec / ck_feat already point at the tile's first pair,
 // or are NULL.  The checkpointed record is the backward's 20-word layout with the weights premultiplied by the
 // part weight: 0..2 offsets, 3 part | active index << 8, 4..15 weights, 16 1/part weight (0 if the weight is 0),
@@ -348,7 +352,7 @@ __device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& 
 template <typename T>
 __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, float* X, const float* s_part,
                                               const enarf_scene_t& sc, int b, int a, int np, int lane,
-                                              float* __restrict__ ck_rec = nullptr, float* __restrict__ ck_feat = nullptr) {
+                                              float* __restrict__ ck_rec, float* __restrict__ ck_feat FWD_TIMER_PARAM) {
     const int H = sc.H, W = sc.W;
     const float* prob = sc.prob_planes + (size_t)b * sc.prob_batch_stride;
     const int lane8 = lane & 7, grp = lane >> 3;
@@ -400,6 +404,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
             }
         }
         __syncwarp();
+        FWD_PHASE(1);   // pair set-up
         // ---- gather: 8 lanes per point, the four groups take points q0+grp, q0+grp+4, ... ---------------
         for (int q = q0 + grp; q < q1; q += 4) {
             float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -415,6 +420,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
             *reinterpret_cast<float4*>(X + q * XSW + ((4 * lane8) ^ (8 * (q & 3)))) = f;
         }
         __syncwarp();
+        FWD_PHASE(2);   // gather
         q0 = q1;
     }
 }
