@@ -1,0 +1,24 @@
+"""Per-phase clock64() breakdown of the forward kernels (per warp).  Needs a development build:
+   ENARF_NVCC_EXTRA=-DENARF_PHASE_TIMING python -c "from enarf_gan_b200.build import build_library as b; b(force=True)" """
+import ctypes, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch, bench
+from enarf_gan_b200 import _abi
+dev = torch.device("cuda:0"); torch.cuda.set_device(0)
+w = bench.build_workload(0, 8, dev)
+for i in range(2): bench.step_device(w, i)
+torch.cuda.synchronize()
+lib = _abi.lib()
+buf = (ctypes.c_ulonglong * 8)()
+lib.enarf_debug_fwd_phases(buf, 1)
+n = 3
+for i in range(n): bench.step_device(w, 10 + i)
+torch.cuda.synchronize()
+lib.enarf_debug_fwd_phases(buf, 1)
+names = ["tile prologue", "pair set-up", "gather", "row store + decoder + head", "idle at end of chunk phase",
+         "outputs / compositing + tile-top barrier", "failed chunk claim", "-"]
+tot = sum(buf)
+warps = 296 * 8
+for nm, v in zip(names, buf):
+    if v: print("%-42s %6.2f%%   %.3f ms per warp per pass" % (nm, 100.0 * v / tot, v / n / 2 / warps / 1.965e6))
+print("total %.3f ms per warp per pass (coarse + fine averaged)" % (tot / n / 2 / warps / 1.965e6))
