@@ -1,5 +1,4 @@
-// Decoder MLP (32 -> 64 -> 64 -> 4) for 32 points per warp on the tensor pipe, activations chained through
-// registers.  Replaces libraries/NeRF/net.py:10-27 (StyledMLP) applied point-wise
+// Decoder MLP (32 -> 64 -> 64 -> 4) for 32 points per warp on the tensor pipe.  Replaces libraries/NeRF/net.py:10-27 (StyledMLP) applied point-wise
 // (libraries/triplane/triplane_nerf.py:44-47) with W_eff / bias supplied per sample.
 //
 // Precision: the parity bar is 1e-4 on fp32 outputs, so every product is the error-compensated 3xTF32 form
@@ -13,7 +12,10 @@
 // directly as the A fragment of the next layer's k-block by choosing the k permutation
 //   logical k = t  <->  channel 8j+2t,   logical k = t+4  <->  channel 8j+2t+1
 // and loading the B fragment (weights) with the same permutation: one 64-bit load W[n][8j+2t .. 8j+2t+1].
-// Layer 2's output is consumed n-tile by n-tile as k-blocks of layer 3, so it never materialises.
+// Layers 1 and 2 each keep all 8 n-tiles x 2 m-tiles in flight (16 independent accumulator chains: one n-tile at
+// a time leaves 4 chains of dependent mma and the tensor pipe idle).  Two such accumulator sets do not fit in 128
+// registers, so layer 1's activations are parked in the warp's own slab (fragment layout in, same layout out:
+// the k permutation above still applies), and layer 2's accumulators feed layer 3 straight from registers.
 #pragma once
 #include "common.cuh"
 #include "gather.cuh"

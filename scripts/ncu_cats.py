@@ -23,7 +23,7 @@ MARK = {
     "gather.cuh": [("float lrelu_s2(", "lrelu"), ("float unit_bin(", "unit_bin"), ("float4 load_feat4(", "texel load (LDG + address)"),
                    ("float4 gather_point(", "gather_point")],
     "mlp_mma.cuh": [("load_decoder_mma(", "load decoder"), ("void mma_tf32(", "mma + split helpers"),
-                    ("void decode32_mma(", "decoder L1"), ("layer 2 (64 -> 64)", "decoder L2+L3")],
+                    ("void decode32_mma(", "decoder L1"), ("layer-1 activations -> the warp", "decoder A1 store"), ("---- layer 2: 64 -> 64", "decoder L2+L3")],
     "mma_smem.cuh": [("struct FragA", "bwd mma: fragment loads + split"), ("void mma3_tiles(", "bwd mma: mma issue"),
                      ("void gemm_pts_mma(", "bwd mma: gemm loop"), ("void wgrad_mma(", "bwd mma: wgrad loop")],
 }
