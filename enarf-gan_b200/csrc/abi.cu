@@ -14,7 +14,7 @@ void enarf_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* enarf_last_error(void) { return g_err; }
-extern "C" int enarf_version(void) { return 130; }
+extern "C" int enarf_version(void) { return 140; }
 
 int enarf_sm_count() {
     static int sms = 0;

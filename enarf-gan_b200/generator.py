@@ -95,3 +95,125 @@ class TriNARFGenerator(nn.Module):
         if return_bg:
             return fg_color, fg_mask, bg_color
         return rendered_color, fg_mask, fine_weights, fine_depth
+
+
+def mask_based_sampler(mask: torch.Tensor, ray_batchsize: int, generator: Optional[torch.Generator] = None):
+    """DSO ray selection (libraries/NeRF/ray_sampler.py:7-39): dilate the foreground mask with a 129 x 129 max-pool,
+    add U(0,1) noise and keep the ``ray_batchsize`` largest pixels of every image.
+    mask (B,h,w) -> (ray_idx (B,ray_bs) int64 flat pixel ids, homo_img (B,1,3,ray_bs) pixel centres)."""
+    batchsize, h, w = mask.shape
+    pad_size = 64
+    m = torch.nn.functional.max_pool2d(mask.float(), pad_size * 2 + 1, stride=1, padding=pad_size)
+    m = m.reshape(batchsize, h * w)
+    m = m + torch.empty_like(m).uniform_(generator=generator)
+    ray_idx = torch.topk(m, ray_batchsize, dim=1, sorted=False)[1]
+    x = ray_idx % w
+    y = torch.div(ray_idx, w, rounding_mode="floor")
+    rays = (torch.stack([x, y], dim=2) + 0.5).permute(0, 2, 1)
+    homo_img = torch.cat([rays, torch.ones(batchsize, 1, ray_batchsize, device=mask.device)], dim=1)
+    return ray_idx, homo_img.reshape(batchsize, 1, 3, -1)
+
+
+class DSONARFGenerator(nn.Module):
+    """Dynamic-scene-overfitting generator (models/generator.py:143-278) for the tri-plane ("denarf") model:
+    time / pose conditioned latents -> deformation-field tri-plane -> sparse render of ``ray_batchsize`` rays per
+    image chosen by ``mask_based_sampler``.  ``flow_generator`` is the injected flow head (the reference builds a
+    StyleGAN2-ADA network there, outside this path)."""
+
+    def __init__(self, config, size, num_bone=1, parent_id=None, num_bone_param=None,
+                 flow_generator: Optional[nn.Module] = None, tri_plane_gen: Optional[nn.Module] = None,
+                 plane_dtype=torch.float32):
+        super().__init__()
+        self.config = config
+        self.size = size
+        self.num_bone = num_bone
+        self.ray_sampler = mask_based_sampler
+        if not _cfg(config, "use_triplane"):
+            raise NotImplementedError("MLPNARF (use_triplane: False) is outside the tri-plane hot path")
+        nerf_params = _cfg(config, "nerf_params")
+        self.time_conditional = _cfg(nerf_params, "time_conditional")
+        self.pose_conditional = _cfg(nerf_params, "pose_conditional")
+        z_dim = (20 if self.time_conditional else 0) + ((num_bone - 1) * 9 if self.pose_conditional else 0)
+        if _cfg(nerf_params, "origin_location") == "center+head":
+            num_bone_param = num_bone
+        view_dependent = not _cfg(nerf_params, "no_ray_direction")
+        self.nerf = TriPlaneNARF(nerf_params, z_dim=z_dim, num_bone=num_bone, bone_length=True, parent=parent_id,
+                                 num_bone_param=num_bone_param, view_dependent=view_dependent,
+                                 tri_plane_gen=tri_plane_gen, plane_dtype=plane_dtype, flow_generator=flow_generator)
+
+    def register_canonical_pose(self, pose: np.ndarray):
+        self.nerf.register_canonical_pose(pose)
+
+    @staticmethod
+    def positional_encoding(x: torch.Tensor, num_frequency: int) -> torch.Tensor:
+        """(B,) -> (B, 2*num_frequency): cos then sin of x * 2^i * pi."""
+        x = x[:, None] * 2 ** torch.arange(num_frequency, device=x.device) * np.pi
+        return torch.cat([torch.cos(x), torch.sin(x)], dim=1)
+
+    @staticmethod
+    def pose_encoding(pose: torch.Tensor):
+        """(B,num_bone,4,4) -> (B,(num_bone-1)*9): every joint rotation relative to the root's."""
+        rot = pose[:, 1:, :3, :3]
+        root_rot = pose[:, :1, :3, :3]
+        encoded = torch.matmul(root_rot.permute(0, 1, 3, 2), rot)
+        return encoded.reshape(encoded.shape[0], -1)
+
+    def get_latents(self, frame_time: torch.Tensor, pose_to_camera: torch.Tensor):
+        zs = []
+        if self.time_conditional:
+            zs.append(self.positional_encoding(frame_time, num_frequency=10))
+        if self.pose_conditional:
+            zs.append(self.pose_encoding(pose_to_camera))
+        assert len(zs) > 0
+        z = torch.cat(zs, dim=1)
+        return z, z
+
+    def forward(self, pose_to_camera, camera_pose, mask, frame_time, bone_length, inv_intrinsics,
+                background: Optional[float] = None):
+        """-> (rendered_color (B,3,ray_bs), rendered_mask (B,ray_bs), ray_idx (B,ray_bs))."""
+        assert bone_length is not None and pose_to_camera is not None
+        assert isinstance(inv_intrinsics, torch.Tensor)
+        batchsize = pose_to_camera.shape[0]
+        grid, img_coord = self.ray_sampler(mask, _cfg(self.config, "ray_batchsize"))
+        z1, z2 = self.get_latents(frame_time, pose_to_camera)
+        nparams = _cfg(self.config, "nerf_params")
+        color, rendered_mask = self.nerf(batchsize, img_coord, pose_to_camera, inv_intrinsics, z1, z2, bone_length,
+                                         Nc=_cfg(nparams, "Nc"), Nf=_cfg(nparams, "Nf"), return_intermediate=False,
+                                         camera_pose=camera_pose)
+        if background is None:
+            background = -1
+        color = color + background * (1 - rendered_mask[:, None])
+        return color, rendered_mask, grid
+
+    def render_entire_img(self, pose_to_camera, inv_intrinsics, frame_time, bone_length, camera_pose=None,
+                          render_size=128, semantic_map=False, use_normalized_intrinsics=False, no_grad=True,
+                          bbox=None):
+        z1, z2 = self.get_latents(frame_time, pose_to_camera)
+        nparams = _cfg(self.config, "nerf_params")
+        return self.nerf.render_entire_img(pose_to_camera, inv_intrinsics, z1, z2, bone_length, camera_pose,
+                                           render_size, _cfg(nparams, "Nc"), _cfg(nparams, "Nf"), semantic_map,
+                                           use_normalized_intrinsics, no_grad=no_grad, bbox=bbox)
+
+
+class PhotometricLoss:
+    """Sparse photometric loss of the DSO step (libraries/NeRF/loss.py:5-48): gather the ground-truth pixels at the
+    sampled ray ids, then MSE or truncated MAE on colour and MSE on the mask."""
+
+    def __init__(self, config):
+        self.config = config
+
+    def __call__(self, grid, sparse_color, sparse_mask, color, mask=None):
+        batchsize, _, size, _ = color.shape
+        sampled_color = torch.gather(color.reshape(batchsize, 3, size * size), 2, grid[:, None].expand(-1, 3, -1))
+        sampled_mask = torch.gather(mask.reshape(batchsize, size * size), 1, grid) if mask is not None else None
+        kind = _cfg(self.config, "nerf_loss_type")
+        if kind == "mse":
+            loss_color = torch.nn.functional.mse_loss(sampled_color, sparse_color)
+        elif kind == "mae":
+            loss_color = torch.clamp_min(torch.abs(sampled_color - sparse_color), 0.01).mean()
+        else:
+            raise ValueError(kind)
+        loss_color = loss_color * _cfg(self.config, "color_coef")
+        loss_mask = torch.nn.functional.mse_loss(sampled_mask, sparse_mask) * _cfg(self.config, "mask_coef") \
+            if sampled_mask is not None else 0
+        return loss_color, loss_mask

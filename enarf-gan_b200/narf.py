@@ -18,7 +18,7 @@ from torch import nn
 from . import hostmath, ops, rendering
 
 _UNSUPPORTED = ("selector_mlp", "no_selector", "clamp_mask", "multiply_density_with_triplane_wieght",
-                "constant_trimask", "deformation_field")
+                "constant_trimask")
 
 
 class EqualLinear(nn.Module):
@@ -88,7 +88,7 @@ class TriPlaneNARF(nn.Module):
 
     def __init__(self, config, z_dim=256, num_bone=1, bone_length=True, parent=None, num_bone_param=None,
                  view_dependent: bool = False, tri_plane_gen: Optional[nn.Module] = None,
-                 plane_dtype=torch.float32):
+                 plane_dtype=torch.float32, flow_generator: Optional[nn.Module] = None):
         super().__init__()
         assert bone_length and parent is not None
         if view_dependent:
@@ -111,8 +111,18 @@ class TriPlaneNARF(nn.Module):
         self.rng_seed = 0
         self.temporal_state = {}
         self.buffers_tensors = {}
+        self.deformation_field = False
         if _cfg(config, "constant_triplane", False):
             self.tri_plane = nn.Parameter(torch.zeros(1, 32 * 3 + self.num_bone * 3, 256, 256))
+        elif _cfg(config, "deformation_field", False):
+            # DSO "denarf" (narf.py:39-58): one canonical tri-plane, warped per sample by a 6-channel flow field.
+            # The flow head itself is the StyleGAN2-ADA generator (out of scope): pass it as ``flow_generator``
+            # (called as flow_generator(z, bone_length, truncation_psi=...) -> (B,6,256,256)) or hand the flow
+            # over as model_input["flow"].
+            self.deformation_field = True
+            self.tri_plane = nn.Parameter(torch.zeros(1, 32 * 3 + self.num_bone * 3, 256, 256))
+            if flow_generator is not None:
+                self.flow_generator = flow_generator
         elif tri_plane_gen is not None:
             self.tri_plane_gen = tri_plane_gen     # e.g. the StyleGAN2-ADA generator (out of scope here)
         self.mlp = StyledMLP(32, 64, 4, style_dim=self.z2_dim)
@@ -131,7 +141,27 @@ class TriPlaneNARF(nn.Module):
         return hostmath.part_frames(pose_to_camera, bone_length, self.origin_location, self.parent_id)
 
     # ---- tri-plane ------------------------------------------------------------------------------------
+    def compute_flow(self, z, bone_length, truncation_psi=1):
+        if not hasattr(self, "flow_generator"):
+            raise RuntimeError("deformation_field needs a flow_generator module or model_input['flow']")
+        return self.flow_generator(z, bone_length, truncation_psi=truncation_psi)
+
+    def warped_planes(self, flow):
+        """flow (B,6,H,W) -> (feature planes (B,3,H,W,32) channels-last in ``plane_dtype``, probability planes
+        (1,3P,H,W)): the deformation-field producer (narf.py:43-57) emitting the renderer's own layout."""
+        canon = ops.RepackCanonical.apply(self.tri_plane)
+        return ops.warp_planes(canon, flow, self.plane_dtype), self.tri_plane[:, 32 * 3:]
+
     def compute_tri_plane_feature(self, z, bone_length, truncation_psi=1):
+        if self.deformation_field:
+            # the reference's NCHW result (narf.py:55-57), for callers that want the tensor itself; the render path
+            # (build_scene) hands the channels-last planes over without building this
+            B = z.shape[0]
+            feat = ops.warp_planes(ops.RepackCanonical.apply(self.tri_plane),
+                                   self.compute_flow(z, bone_length, truncation_psi))
+            H, W = feat.shape[2:4]
+            warped = feat.permute(0, 1, 4, 2, 3).reshape(B, 32 * 3, H, W)
+            return torch.cat([warped, self.tri_plane[:, 32 * 3:].expand(B, -1, -1, -1)], dim=1)
         if hasattr(self, "tri_plane"):
             return self.tri_plane.expand(z.shape[0], -1, -1, -1)
         if not hasattr(self, "tri_plane_gen"):
@@ -143,14 +173,24 @@ class TriPlaneNARF(nn.Module):
         """SceneBuffers for one render call + the autograd-tracked tensors behind it."""
         bone_length, z, z_rend = model_input["bone_length"], model_input["z"], model_input["z_rend"]
         tri_plane = model_input.get("tri_plane_feature")
+        decoder = self.mlp.effective(z_rend)
+        cscale = (self.canonical_bone_length[None, :, None] / bone_length / self.coordinate_scale)[:, :, 0]
+        if self.deformation_field and tri_plane is None:
+            planes = model_input.get("planes")
+            if planes is None:
+                flow = model_input.get("flow")
+                if flow is None:
+                    flow = self.compute_flow(z, bone_length, model_input.get("truncation_psi", 1))
+                planes = self.warped_planes(flow)
+            scene = ops.SceneBuffers(pose_scaled, cscale, self.canonical_pose, None, decoder,
+                                     feat_planes=planes[0], prob_planes=planes[1])
+            return scene, planes, decoder
         if tri_plane is None:
             tri_plane = self.compute_tri_plane_feature(z, bone_length, model_input.get("truncation_psi", 1))
         tri_plane = tri_plane.to(torch.float32).contiguous()      # materialises an expanded constant plane
         self.buffers_tensors["tri_plane_feature"] = tri_plane      # narf.py:194
         if not self.training:
             self.temporal_state["tri_plane_feature"] = tri_plane
-        decoder = self.mlp.effective(z_rend)
-        cscale = (self.canonical_bone_length[None, :, None] / bone_length / self.coordinate_scale)[:, :, 0]
         scene = ops.SceneBuffers(pose_scaled, cscale, self.canonical_pose, tri_plane, decoder, self.plane_dtype)
         return scene, tri_plane, decoder
 
@@ -182,6 +222,9 @@ class TriPlaneNARF(nn.Module):
                           no_grad=True, truncation_psi=1, bbox=None):
         model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
         pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
-        model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
+        if self.deformation_field:      # same hoisting as NARF/base.py:59-60, in the hand-off layout
+            model_input["planes"] = self.warped_planes(self.compute_flow(z[:1], bone_length[:1], truncation_psi))
+        else:
+            model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
         return rendering.render_entire_img(self, pose_to_camera, inv_intrinsics, camera_pose, render_size, Nc, Nf,
                                            semantic_map, use_normalized_intrinsics, no_grad, model_input, bbox=bbox)

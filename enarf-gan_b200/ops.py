@@ -23,14 +23,27 @@ class SceneBuffers:
     tri_plane (B,(32+P)*3,H,W) NCHW as the reference produces it, decoder = [(W_eff (B,out,in), bias), ...].
     """
 
-    def __init__(self, pose, cscale, canon_pose, tri_plane, decoder, plane_dtype=torch.float32, feat_planes=None):
+    def __init__(self, pose, cscale, canon_pose, tri_plane, decoder, plane_dtype=torch.float32, feat_planes=None,
+                 prob_planes=None):
         B, P = pose.shape[:2]
-        H, W = tri_plane.shape[-2:]
-        assert tri_plane.shape[1] == (FEAT_DIM + P) * 3, "tri-plane must have (32+P)*3 channels"
         f32 = lambda t: t.detach().to(torch.float32).contiguous()
         self.pose, self.cscale, self.canon_pose = f32(pose), f32(cscale), f32(canon_pose)
-        self.tri_plane = tri_plane if (tri_plane.dtype == torch.float32 and tri_plane.is_contiguous()) \
-            else tri_plane.detach().to(torch.float32).contiguous()
+        if tri_plane is None:
+            # producer hand-off (SURVEY 8f N1): channels-last feature planes (B,3,H,W,32) as warp_planes emits them
+            # and NCHW probability planes (B or 1, 3P, H, W); a batch of 1 is shared by every sample (stride 0)
+            assert feat_planes is not None and prob_planes is not None
+            assert feat_planes.shape[0] == B and feat_planes.shape[1] == 3 and feat_planes.shape[4] == FEAT_DIM
+            assert prob_planes.shape[0] in (1, B) and prob_planes.shape[1] == 3 * P
+            assert prob_planes.dtype == torch.float32 and prob_planes[0].is_contiguous()
+            H, W = feat_planes.shape[2:4]
+            assert tuple(prob_planes.shape[-2:]) == (H, W)
+            plane_dtype = feat_planes.dtype
+            self.tri_plane = None
+        else:
+            H, W = tri_plane.shape[-2:]
+            assert tri_plane.shape[1] == (FEAT_DIM + P) * 3, "tri-plane must have (32+P)*3 channels"
+            self.tri_plane = tri_plane if (tri_plane.dtype == torch.float32 and tri_plane.is_contiguous()) \
+                else tri_plane.detach().to(torch.float32).contiguous()
         self.plane_dtype = plane_dtype
         self.B, self.P, self.H, self.W = B, P, H, W
         (w1, b1), (w2, b2), (w3, b3) = decoder
@@ -39,15 +52,21 @@ class SceneBuffers:
         self.b = [f32(b1).reshape(-1), f32(b2).reshape(-1), f32(b3).reshape(-1)]
         if feat_planes is None:
             feat_planes = repack_planes(self.tri_plane.detach(), plane_dtype)
-        self.feat_planes = feat_planes
-        self.prob_view = self.tri_plane.detach()[:, FEAT_DIM * 3:]
+        self.feat_planes = feat_planes.detach()
+        assert self.feat_planes.is_contiguous()
+        if self.tri_plane is None:
+            self.prob_view = prob_planes.detach()
+            prob_stride = 0 if prob_planes.shape[0] == 1 else prob_planes.stride(0)
+        else:
+            self.prob_view = self.tri_plane.detach()[:, FEAT_DIM * 3:]
+            prob_stride = self.tri_plane.stride(0)
         s = _abi.Scene()
         s.B, s.P, s.H, s.W = B, P, H, W
         s.pose, s.cscale, s.canon_pose = ptr(self.pose), ptr(self.cscale), ptr(self.canon_pose)
         s.feat_planes = ptr(self.feat_planes, None)
         s.feat_dtype = _abi.DTYPE_F32 if plane_dtype == torch.float32 else _abi.DTYPE_BF16
         s.prob_planes = self.prob_view.data_ptr()
-        s.prob_batch_stride = self.tri_plane.stride(0)
+        s.prob_batch_stride = prob_stride
         s.w1, s.w2, s.w3 = (ptr(t) for t in self.w)
         s.b1, s.b2, s.b3 = (ptr(t) for t in self.b)
         self.c = s
@@ -71,6 +90,63 @@ def unpack_plane_grads(d_feat, d_tri_plane, accumulate=True):
     B, C, H, W = d_tri_plane.shape
     check(lib().enarf_unpack_plane_grads(ptr(d_feat), B, C, H, W, int(accumulate), ptr(d_tri_plane), stream_ptr()))
     return d_tri_plane
+
+
+class WarpPlanes(torch.autograd.Function):
+    """Deformation-field producer (models/narf.py:39-58) emitting the renderer's layout.  canon_feat (3,H,W,32) fp32
+    channels-last, flow (B,6,H,W) fp32 -> (B,3,H,W,32) in ``dtype``.  The incoming gradient is consumed in the
+    output's dtype (autograd casts it), d_canon_feat is accumulated in fp32."""
+
+    @staticmethod
+    def forward(ctx, canon_feat, flow, dtype):
+        _, H, W, _ = canon_feat.shape
+        B = flow.shape[0]
+        assert flow.shape == (B, 6, H, W) and canon_feat.shape == (3, H, W, FEAT_DIM)
+        canon_feat, flow = canon_feat.contiguous(), flow.to(torch.float32).contiguous()
+        out = torch.empty(B, 3, H, W, FEAT_DIM, device=flow.device, dtype=dtype)
+        check(lib().enarf_warp_planes_fwd(ptr(canon_feat), ptr(flow), B, H, W, ptr(out, None), _dtype_code(dtype),
+                                          stream_ptr()))
+        ctx.save_for_backward(canon_feat, flow)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        canon_feat, flow = ctx.saved_tensors
+        B, _, H, W = flow.shape
+        g = g.contiguous()
+        d_canon = torch.zeros_like(canon_feat) if ctx.needs_input_grad[0] else None
+        d_flow = torch.empty_like(flow) if ctx.needs_input_grad[1] else None
+        if d_canon is not None or d_flow is not None:
+            check(lib().enarf_warp_planes_bwd(ptr(g, None), _dtype_code(g.dtype), ptr(canon_feat), ptr(flow), B, H, W,
+                                              ptr(d_canon, allow_none=True), ptr(d_flow, allow_none=True), stream_ptr()))
+        return d_canon, d_flow, None
+
+
+def _dtype_code(dtype):
+    if dtype == torch.float32:
+        return _abi.DTYPE_F32
+    if dtype == torch.bfloat16:
+        return _abi.DTYPE_BF16
+    raise TypeError(f"plane dtype must be float32 or bfloat16, got {dtype}")
+
+
+def warp_planes(canon_feat, flow, dtype=torch.float32):
+    """canon_feat (3,H,W,32) channels-last fp32, flow (B,6,H,W) -> warped feature planes (B,3,H,W,32)."""
+    return WarpPlanes.apply(canon_feat, flow, dtype)
+
+
+class RepackCanonical(torch.autograd.Function):
+    """(1,C,H,W) NCHW parameter -> (3,H,W,32) channels-last feature planes, with the transposed gradient."""
+
+    @staticmethod
+    def forward(ctx, tri_plane):
+        ctx.shape = tri_plane.shape
+        return repack_planes(tri_plane.detach().to(torch.float32).contiguous())[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        d = torch.zeros(ctx.shape, device=g.device)
+        return unpack_plane_grads(g.contiguous().float()[None], d, accumulate=False)
 
 
 def near_far(pose, near0=0.3, far0=5.0):
@@ -250,6 +326,55 @@ class RenderFine(torch.autograd.Function):
                 db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
 
 
+class RenderFinePlanes(torch.autograd.Function):
+    """Fused fine pass on handed-over planes: feat_planes (B,3,H,W,32) channels-last (fp32 / bf16) and prob_planes
+    (B or 1, 3P, H, W) NCHW.  The gradients come back in the same layouts -- d_feat exactly as the kernel
+    accumulates it (no unpack), d_prob summed over the batch when the planes are shared."""
+
+    @staticmethod
+    def forward(ctx, scene, dmin, dmax, direction, bins, feat_planes, prob_planes, w1, w2, w3, b1, b2, b3):
+        pairs_on = SAVE_FEATURES and PAIR_CKPT
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
+                               want_pairs=pairs_on)
+        ctx.scene = scene
+        saved = [dmin, dmax, direction, bins, out[5]]
+        if SAVE_FEATURES:
+            saved.append(out[6])
+        if pairs_on:
+            saved.extend(out[7].tensors())
+        ctx.has_feat, ctx.has_pairs = SAVE_FEATURES, pairs_on
+        ctx.save_for_backward(*saved)
+        ctx.prob_shape = prob_planes.shape
+        out = out[:6]
+        ctx.mark_non_differentiable(out[4], out[5])
+        return out
+
+    @staticmethod
+    def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
+        scene = ctx.scene
+        dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
+        feat = rest.pop(0) if ctx.has_feat else None
+        pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
+        B, n, Nf = bins.shape
+        dev = bins.device
+        c = lambda g: None if g is None else g.contiguous().float()
+        d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
+        d_prob = torch.zeros(ctx.prob_shape, device=dev)
+        stride = 0 if ctx.prob_shape[0] == 1 else d_prob.stride(0)
+        dw = [torch.zeros_like(w) for w in scene.w]
+        db = [torch.zeros_like(b) for b in scene.b]
+        g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
+        check(lib().enarf_render_fine_bwd(
+            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True),
+            pairs.ref if pairs else None, n, Nf,
+            ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
+            ptr(g[3], allow_none=True), ptr(d_feat), ptr(d_prob), stride,
+            ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+        return (None, None, None, None, None, d_feat if ctx.needs_input_grad[5] else None,
+                d_prob if ctx.needs_input_grad[6] else None, dw[0], dw[1], dw[2],
+                db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
+
+
 def ctx_shape(scene, i):
     return scene.b_shapes[i] if hasattr(scene, "b_shapes") else scene.b[i].shape
 
@@ -263,5 +388,8 @@ def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None
         return out if want_points is None or want_points else out + (None,)
     (w1, b1), (w2, b2), (w3, b3) = decoder
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
+    if isinstance(tri_plane, (tuple, list)):        # (feat_planes channels-last, prob_planes NCHW)
+        out = RenderFinePlanes.apply(scene, dmin, dmax, direction, bins, tri_plane[0], tri_plane[1], w1, w2, w3, b1, b2, b3)
+        return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
     out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)
     return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))

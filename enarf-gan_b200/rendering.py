@@ -108,7 +108,9 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
     if _scene is None:
         _scene = model.build_scene(pose_scaled, model_input)
     scene, tri_plane, decoder = _scene
-    track = torch.is_grad_enabled() and (tri_plane.requires_grad or any(w.requires_grad for w, _ in decoder))
+    planes_grad = any(t.requires_grad for t in tri_plane) if isinstance(tri_plane, (tuple, list)) \
+        else tri_plane.requires_grad
+    track = torch.is_grad_enabled() and (planes_grad or any(w.requires_grad for w, _ in decoder))
     out = render_rays(scene, image_coord.reshape(B, 3, n_all), inv_intrinsics, Nc, Nf,
                       rng=getattr(model, "rng_mode", "torch"), seed=getattr(model, "rng_seed", 0),
                       idx=getattr(model, "rng_given", (None, None))[0],

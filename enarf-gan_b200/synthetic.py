@@ -138,3 +138,23 @@ def make_triplane(B: int, num_part: int = 24, seed: int = 1234, res: int = 256, 
 def make_latent(B: int, z_dim: int = 256, n_chunks: int = 3, seed: int = 1234) -> torch.Tensor:
     g = torch.Generator().manual_seed(seed + 77)
     return torch.randn(B, z_dim * n_chunks, generator=g)
+
+
+def make_flow(B: int, seed: int = 1234, res: int = 256, coarse: int = 8, amplitude: float = 4.0) -> torch.Tensor:
+    """Smooth synthetic deformation field ``(B,6,res,res)`` in texels, the shape the DSO flow head emits
+    (``models/narf.py:45-46``: channel 2k / 2k+1 = x / y offset of plane k).  Low-resolution Gaussian noise
+    upsampled bicubically: offsets of a few texels, large enough near the borders to leave the plane."""
+    g = torch.Generator().manual_seed(seed + 991)
+    low = torch.randn(B, 6, coarse, coarse, generator=g) * amplitude
+    return torch.nn.functional.interpolate(low, size=(res, res), mode="bicubic", align_corners=False).contiguous()
+
+
+def make_foreground_mask(B: int, size: int, seed: int = 1234) -> torch.Tensor:
+    """``(B,size,size)`` 0/1 foreground mask: a centred ellipse per sample with a seeded radius."""
+    rng = np.random.RandomState(seed + 5)
+    yy, xx = np.meshgrid(np.arange(size) + 0.5, np.arange(size) + 0.5, indexing="ij")
+    out = np.zeros((B, size, size), dtype=np.float32)
+    for b in range(B):
+        rx, ry = rng.uniform(0.15, 0.3) * size, rng.uniform(0.3, 0.45) * size
+        out[b] = (((xx - size / 2) / rx) ** 2 + ((yy - size / 2) / ry) ** 2 <= 1).astype(np.float32)
+    return torch.from_numpy(out)

@@ -75,6 +75,20 @@ int enarf_repack_planes(const float* tri_plane_nchw, int B, int C_total, int H, 
 int enarf_unpack_plane_grads(const float* d_feat, int B, int C_total, int H, int W, int accumulate,
                              float* d_tri_plane_nchw, void* stream);
 
+/* Deformation-field tri-plane producer of the DSO ("denarf") model (models/narf.py:39-58: flow -> warped grid ->
+ * F.grid_sample of the canonical feature planes, bilinear / zero padding / align_corners=False), emitting the
+ * renderer's own layout so that the warped planes are never built as NCHW nor re-packed.
+ * canon_feat (3,H,W,32) fp32 channels-last (enarf_repack_planes of the (1,C,H,W) parameter); flow (B,6,H,W) fp32 as
+ * the flow head emits it (channel 2k = x offset, 2k+1 = y offset of plane k, in texels); feat_out (B,3,H,W,32) in
+ * out_dtype, directly usable as enarf_scene_t.feat_planes.  W must be a multiple of 4. */
+int enarf_warp_planes_fwd(const float* canon_feat, const float* flow, int B, int H, int W, void* feat_out,
+                          int out_dtype, void* stream);
+/* Gradient of the above.  d_feat (B,3,H,W,32) in d_feat_dtype (the fp32 buffer enarf_render_fine_bwd fills, or bf16).
+ * d_canon_feat (3,H,W,32) fp32 is ADDED into (caller zero-initialises; summed over the batch); d_flow (B,6,H,W) is
+ * STORED.  Either output may be NULL. */
+int enarf_warp_planes_bwd(const void* d_feat, int d_feat_dtype, const float* canon_feat, const float* flow, int B,
+                          int H, int W, float* d_canon_feat, float* d_flow, void* stream);
+
 /* Batch-global near/far (rendering.py:15-17): nearfar[0] = max(min tz - sqrt3, near0),
  * nearfar[1] = max(max tz + sqrt3, far0) over all B*P part translations of `pose`. */
 int enarf_near_far(const float* pose, int B, int P, float near0, float far0, float* nearfar, void* stream);

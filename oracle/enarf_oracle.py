@@ -224,6 +224,29 @@ def triplane_sample_sum(tri_plane, position):
     return out
 
 
+def warp_triplane(tri_plane, flow, feat_dim=32):
+    """Deformation-field tri-plane producer of the DSO model (models/narf.py:43-57).
+    tri_plane (1,(feat_dim+P)*3,S,S) canonical planes; flow (B,6,S,S) = the flow head's output, channel 2k / 2k+1
+    the x / y offset (in texels) of plane k.  grid = (pixel centre + flow) / (S/2) - 1 (narf.py:49; the reference
+    writes the 128 of S = 256), every feature plane is resampled there (bilinear, zeros, align_corners=False), the
+    probability planes are passed through unchanged.  -> (B,(feat_dim+P)*3,S,S)."""
+    B = flow.shape[0]
+    S = tri_plane.shape[-1]
+    dt = tri_plane.dtype
+    ar = torch.arange(S, dtype=dt) + 0.5
+    gx = ar[None, :].expand(S, S).reshape(-1)
+    gy = ar[:, None].expand(S, S).reshape(-1)
+    fl = flow.to(dt).reshape(B, 3, 2, S * S)
+    planes = []
+    for b in range(B):
+        for k in range(3):
+            x = (gx + fl[b, k, 0]) / (S / 2) - 1
+            y = (gy + fl[b, k, 1]) / (S / 2) - 1
+            planes.append(bilinear_zeros(tri_plane[0, k * feat_dim:(k + 1) * feat_dim], x, y))
+    warped = torch.stack(planes).reshape(B, 3 * feat_dim, S, S)
+    return torch.cat([warped, tri_plane[:, 3 * feat_dim:].expand(B, -1, -1, -1)], dim=1)
+
+
 def gather_features(tri_plane, canon, valid, feat_dim=32):
     """tri_plane (B,(feat_dim+P)*3,H,W); canon (B,P,3,N); valid (B,P,N)
     -> feature (B,feat_dim,N), part weight (B,P,N) (zero where invalid).
