@@ -172,7 +172,14 @@ def test_dso_step_gradients(name, plane_dtype, tol):
             L[k].requires_grad_()
     c_ref = canon.clone().requires_grad_()
     f_ref = flow.clone().requires_grad_()
-    sc = O.Scene(inp["pose_to_camera"], inp["bone_length"], inp["inv_intrinsics"], O.warp_triplane(c_ref, f_ref),
+    warped = O.warp_triplane(c_ref, f_ref)
+    if plane_dtype == torch.bfloat16:
+        # bf16 planes move the point the gradient is taken at (activation kinks flip: a few % of the max-norm), which
+        # says nothing about the kernels: the oracle renders the same bf16-rounded feature planes (straight-through),
+        # so what is compared is the backward arithmetic incl. the bf16 rounding of the plane gradient
+        feat = warped[:, :96]
+        warped = torch.cat([feat + (feat.bfloat16().float() - feat).detach(), warped[:, 96:]], dim=1)
+    sc = O.Scene(inp["pose_to_camera"], inp["bone_length"], inp["inv_intrinsics"], warped,
                  layers, z, S.canonical_pose(), S.SMPL_PARENTS, origin_location="center_fixed", coordinate_scale=3.0)
     ref = O.render(sc, img, Nc, Nf, rng)
     up = torch.randn(ref["color"].shape, generator=torch.Generator().manual_seed(9))
