@@ -66,25 +66,36 @@ __device__ __forceinline__ void red4(float* addr, float4 v) {
                  : "memory");
 }
 
-// texels = B*3*H*W output texels; canon (3,H,W,32) fp32; flow (B,6,H,W): channel 2k = x offset, 2k+1 = y offset
-// of plane k (narf.py:46: reshape(bs*3, 2, H, W)).
+// canon (3,H,W,32) fp32; flow (B,6,H,W): channel 2k = x offset, 2k+1 = y offset of plane k (narf.py:46:
+// reshape(bs*3, 2, H, W)); blockIdx.z = b*3 + k.
+// Work decomposition (forward and backward): a CTA owns a strip of 32 columns x WARP_ROWS rows of one (sample, plane);
+// warp w walks columns 4w..4w+3 down the rows.  Flows are smooth, so the source row y0+1 read for output row y is the
+// row y0 of output row y+1 and is still in L1: ~1.1 source lines come from L2 per output texel instead of ~2.1 with
+// row-major CTAs (which made the kernel L2-bandwidth-bound).  The next row's flow is requested one row ahead so the
+// flow -> address -> texel chain costs one memory round trip per row, not two.
+#define WARP_ROWS 16
 template <typename T>
 __global__ void __launch_bounds__(256) warp_fwd_kernel(const float* __restrict__ canon, const float* __restrict__ flow,
-                                                       int H, int W, long long texels, T* __restrict__ out) {
+                                                       int H, int W, T* __restrict__ out) {
     const int HW = H * W;
     const int sub = threadIdx.x & 7;
-    const long long step = (long long)gridDim.x * 32;
-    for (long long t = (long long)blockIdx.x * 32 + (threadIdx.x >> 3); t < texels; t += step) {
-        const long long bk = t / HW;
-        const int yx = (int)(t - bk * HW);
-        const int y = yx / W, x = yx - y * W;
-        const int k = (int)(bk % 3);
-        const float* fl = flow + (size_t)(2 * bk) * HW + yx;
-        const Foot f = footprint(x, y, __ldg(fl), __ldg(fl + HW), H, W);
-        const float* src = canon + (size_t)k * HW * FEAT + 4 * sub;
+    const int x = blockIdx.x * 32 + (threadIdx.x >> 3);
+    const int y_begin = blockIdx.y * WARP_ROWS, y_end = min(H, y_begin + WARP_ROWS);
+    const int bk = blockIdx.z, k = bk % 3;
+    if (x >= W) return;
+    const float* fl = flow + (size_t)(2 * bk) * HW + x;
+    const float* src = canon + (size_t)k * HW * FEAT + 4 * sub;
+    T* dst = out + ((size_t)bk * HW + x) * FEAT + 4 * sub;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    float fx = __ldg(fl + (size_t)y_begin * W), fy = __ldg(fl + HW + (size_t)y_begin * W);
+    for (int y = y_begin; y < y_end; ++y) {
+        const Foot f = footprint(x, y, fx, fy, H, W);
+        if (y + 1 < y_end) {
+            fx = __ldg(fl + (size_t)(y + 1) * W);
+            fy = __ldg(fl + HW + (size_t)(y + 1) * W);
+        }
         const bool xin0 = (unsigned)f.x0 < (unsigned)W, xin1 = (unsigned)(f.x0 + 1) < (unsigned)W;
         const bool yin0 = (unsigned)f.y0 < (unsigned)H, yin1 = (unsigned)(f.y0 + 1) < (unsigned)H;
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         const size_t o00 = ((size_t)f.y0 * W + f.x0) * FEAT;
         // all four loads issued before the first use
         const float4 v00 = (yin0 && xin0) ? load4(src + o00) : z;
@@ -98,7 +109,7 @@ __global__ void __launch_bounds__(256) warp_fwd_kernel(const float* __restrict__
         r.y = v00.y * w00 + v01.y * w01 + v10.y * w10 + v11.y * w11;
         r.z = v00.z * w00 + v01.z * w01 + v10.z * w10 + v11.z * w11;
         r.w = v00.w * w00 + v01.w * w01 + v10.w * w10 + v11.w * w11;
-        store4(out + (size_t)t * FEAT + 4 * sub, r);
+        store4(dst + (size_t)y * W * FEAT, r);
     }
 }
 
@@ -109,40 +120,37 @@ __device__ __forceinline__ float4 scale4(float4 a, float s) { return make_float4
 // d_flow (B,6,H,W) stored.  d(source index)/d(flow) = (size/2) / (size/2) = 1 on both axes.
 template <typename G>
 __global__ void __launch_bounds__(256) warp_bwd_kernel(const G* __restrict__ d_out, const float* __restrict__ canon,
-                                                       const float* __restrict__ flow, int H, int W, long long texels,
+                                                       const float* __restrict__ flow, int H, int W,
                                                        float* __restrict__ d_canon, float* __restrict__ d_flow) {
     const int HW = H * W;
     const int sub = threadIdx.x & 7;
-    const long long step = (long long)gridDim.x * 32;
-    // every lane of a warp runs the same number of iterations (texels is a multiple of 4: H*W*3*B with W % 4 == 0
-    // is required by the host), so the shuffles below are convergent
-    for (long long t = (long long)blockIdx.x * 32 + (threadIdx.x >> 3); t < texels; t += step) {
-        const long long bk = t / HW;
-        const int yx = (int)(t - bk * HW);
-        const int y = yx / W, x = yx - y * W;
-        const int k = (int)(bk % 3);
-        const float* fl = flow + (size_t)(2 * bk) * HW + yx;
-        const Foot f = footprint(x, y, __ldg(fl), __ldg(fl + HW), H, W);
-        const float4 g = load4(d_out + (size_t)t * FEAT + 4 * sub);
-        const size_t base = (size_t)k * HW * FEAT + 4 * sub;
+    const int x = blockIdx.x * 32 + (threadIdx.x >> 3);
+    const int y_begin = blockIdx.y * WARP_ROWS, y_end = min(H, y_begin + WARP_ROWS);
+    const int bk = blockIdx.z, k = bk % 3;
+    if (x >= W) return;   // W % 4 == 0 (checked by the host): a warp's 4 texels are all inside or all outside
+    const float* fl = flow + (size_t)(2 * bk) * HW + x;
+    const G* gsrc = d_out + ((size_t)bk * HW + x) * FEAT + 4 * sub;
+    const size_t base = (size_t)k * HW * FEAT + 4 * sub;
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    float fx = __ldg(fl + (size_t)y_begin * W), fy = __ldg(fl + HW + (size_t)y_begin * W);
+    for (int y = y_begin; y < y_end; ++y) {
+        const Foot f = footprint(x, y, fx, fy, H, W);
+        if (y + 1 < y_end) {
+            fx = __ldg(fl + (size_t)(y + 1) * W);
+            fy = __ldg(fl + HW + (size_t)(y + 1) * W);
+        }
+        const float4 g = load4(gsrc + (size_t)y * W * FEAT);
         const bool xin0 = (unsigned)f.x0 < (unsigned)W, xin1 = (unsigned)(f.x0 + 1) < (unsigned)W;
         const bool yin0 = (unsigned)f.y0 < (unsigned)H, yin1 = (unsigned)(f.y0 + 1) < (unsigned)H;
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         const size_t o00 = base + ((size_t)f.y0 * W + f.x0) * FEAT;
         const size_t o01 = o00 + FEAT, o10 = o00 + (size_t)W * FEAT, o11 = o10 + FEAT;
         const bool in00 = yin0 && xin0, in01 = yin0 && xin1, in10 = yin1 && xin0, in11 = yin1 && xin1;
-        const float4 v00 = in00 ? load4(canon + o00) : z;
-        const float4 v01 = in01 ? load4(canon + o01) : z;
-        const float4 v10 = in10 ? load4(canon + o10) : z;
-        const float4 v11 = in11 ? load4(canon + o11) : z;
         const float wx0 = 1.f - f.wx1, wy0 = 1.f - f.wy1;
-        if (d_canon) {
-            if (in00) red4(d_canon + o00, scale4(g, wx0 * wy0));
-            if (in01) red4(d_canon + o01, scale4(g, f.wx1 * wy0));
-            if (in10) red4(d_canon + o10, scale4(g, wx0 * f.wy1));
-            if (in11) red4(d_canon + o11, scale4(g, f.wx1 * f.wy1));
-        }
         if (d_flow) {
+            const float4 v00 = in00 ? load4(canon + o00) : z;
+            const float4 v01 = in01 ? load4(canon + o01) : z;
+            const float4 v10 = in10 ? load4(canon + o10) : z;
+            const float4 v11 = in11 ? load4(canon + o11) : z;
             const float d00 = dot4(g, v00), d01 = dot4(g, v01), d10 = dot4(g, v10), d11 = dot4(g, v11);
             float gx = (d01 - d00) * wy0 + (d11 - d10) * f.wy1;
             float gy = (d10 - d00) * wx0 + (d11 - d01) * f.wx1;
@@ -152,18 +160,18 @@ __global__ void __launch_bounds__(256) warp_bwd_kernel(const G* __restrict__ d_o
                 gy += __shfl_xor_sync(0xffffffffu, gy, m);
             }
             if (sub == 0) {
-                float* o = d_flow + (size_t)(2 * bk) * HW + yx;
+                float* o = d_flow + (size_t)(2 * bk) * HW + (size_t)y * W + x;
                 o[0] = gx;
                 o[HW] = gy;
             }
         }
+        if (d_canon) {
+            if (in00) red4(d_canon + o00, scale4(g, wx0 * wy0));
+            if (in01) red4(d_canon + o01, scale4(g, f.wx1 * wy0));
+            if (in10) red4(d_canon + o10, scale4(g, wx0 * f.wy1));
+            if (in11) red4(d_canon + o11, scale4(g, f.wx1 * f.wy1));
+        }
     }
-}
-
-int warp_grid(long long texels) {
-    const long long want = (texels + 31) / 32;
-    const long long cap = (long long)enarf_sm_count() * 8 * 4;   // 8 resident CTAs per SM x 4 waves
-    return (int)(want < cap ? want : cap);
 }
 
 }  // namespace
@@ -173,12 +181,12 @@ extern "C" int enarf_warp_planes_fwd(const float* canon_feat, const float* flow,
     ENARF_REQUIRE(canon_feat && flow && feat_out && B > 0 && H > 0 && W > 0, ENARF_ERR_INVALID_ARG,
                   "enarf_warp_planes_fwd: bad arguments");
     ENARF_REQUIRE(W % 4 == 0, ENARF_ERR_UNSUPPORTED, "enarf_warp_planes_fwd: W=%d must be a multiple of 4", W);
-    const long long texels = (long long)B * 3 * H * W;
-    const int grid = warp_grid(texels);
+    ENARF_REQUIRE(3LL * B <= 65535, ENARF_ERR_UNSUPPORTED, "enarf_warp_planes_fwd: batch %d too large", B);
+    const dim3 grid((W + 31) / 32, (H + WARP_ROWS - 1) / WARP_ROWS, 3 * B);
     if (out_dtype == ENARF_DTYPE_F32)
-        warp_fwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(canon_feat, flow, H, W, texels, (float*)feat_out);
+        warp_fwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(canon_feat, flow, H, W, (float*)feat_out);
     else if (out_dtype == ENARF_DTYPE_BF16)
-        warp_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(canon_feat, flow, H, W, texels,
+        warp_fwd_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>(canon_feat, flow, H, W,
                                                                                (__nv_bfloat16*)feat_out);
     else
         ENARF_REQUIRE(false, ENARF_ERR_INVALID_ARG, "enarf_warp_planes_fwd: bad out_dtype %d", out_dtype);
@@ -191,14 +199,14 @@ extern "C" int enarf_warp_planes_bwd(const void* d_feat, int d_feat_dtype, const
     ENARF_REQUIRE(d_feat && canon_feat && flow && (d_canon_feat || d_flow) && B > 0 && H > 0 && W > 0,
                   ENARF_ERR_INVALID_ARG, "enarf_warp_planes_bwd: bad arguments");
     ENARF_REQUIRE(W % 4 == 0, ENARF_ERR_UNSUPPORTED, "enarf_warp_planes_bwd: W=%d must be a multiple of 4", W);
-    const long long texels = (long long)B * 3 * H * W;
-    const int grid = warp_grid(texels);
+    ENARF_REQUIRE(3LL * B <= 65535, ENARF_ERR_UNSUPPORTED, "enarf_warp_planes_bwd: batch %d too large", B);
+    const dim3 grid((W + 31) / 32, (H + WARP_ROWS - 1) / WARP_ROWS, 3 * B);
     if (d_feat_dtype == ENARF_DTYPE_F32)
-        warp_bwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)d_feat, canon_feat, flow, H, W, texels,
+        warp_bwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)d_feat, canon_feat, flow, H, W,
                                                                        d_canon_feat, d_flow);
     else if (d_feat_dtype == ENARF_DTYPE_BF16)
         warp_bwd_kernel<__nv_bfloat16><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)d_feat, canon_feat,
-                                                                               flow, H, W, texels, d_canon_feat, d_flow);
+                                                                               flow, H, W, d_canon_feat, d_flow);
     else
         ENARF_REQUIRE(false, ENARF_ERR_INVALID_ARG, "enarf_warp_planes_bwd: bad d_feat_dtype %d", d_feat_dtype);
     ENARF_CHECK_LAUNCH("enarf_warp_planes_bwd");
