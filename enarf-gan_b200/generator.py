@@ -103,7 +103,9 @@ def mask_based_sampler(mask: torch.Tensor, ray_batchsize: int, generator: Option
     mask (B,h,w) -> (ray_idx (B,ray_bs) int64 flat pixel ids, homo_img (B,1,3,ray_bs) pixel centres)."""
     batchsize, h, w = mask.shape
     pad_size = 64
-    m = torch.nn.functional.max_pool2d(mask.float(), pad_size * 2 + 1, stride=1, padding=pad_size)
+    # a square max-pool is separable: two 1-D passes give the identical dilation at 2*129 instead of 129^2 taps
+    m = torch.nn.functional.max_pool2d(mask.float()[:, None], (pad_size * 2 + 1, 1), stride=1, padding=(pad_size, 0))
+    m = torch.nn.functional.max_pool2d(m, (1, pad_size * 2 + 1), stride=1, padding=(0, pad_size))[:, 0]
     m = m.reshape(batchsize, h * w)
     m = m + torch.empty_like(m).uniform_(generator=generator)
     ray_idx = torch.topk(m, ray_batchsize, dim=1, sorted=False)[1]
