@@ -59,6 +59,7 @@ def build(mode, canon, flow):
                        time_conditional=True, pose_conditional=True, render_bs=16384,
                        deformation_field=(mode == "handoff"))
     config = dict(use_triplane=True, ray_batchsize=size * size, nerf_params=nerf_params)
+    torch.manual_seed(1238)          # same random-init decoder for both producers
     kw = dict(flow_generator=Flow(flow)) if mode == "handoff" else dict(tri_plane_gen=TorchWarp(canon, flow))
     gen = DSONARFGenerator(config, size, num_bone=24, parent_id=S.SMPL_PARENTS, num_bone_param=23,
                            plane_dtype=torch.bfloat16, **kw)
@@ -102,7 +103,7 @@ def main():
         print(json.dumps({"producer": mode, "B": B, "rays": R, "samples_per_ray": 2 * NS, "planes": "bf16",
                           "fwd_ms": round(fwd, 2), "bwd_ms": round(bwd, 2), "step_ms": round(fwd + bwd, 2),
                           "rays_per_s": round(R / (fwd + bwd) * 1e3), "points_per_s": round(R * 2 * NS / (fwd + bwd) * 1e3),
-                          "loss": round(float(lc + lm), 5), "mask_mean": round(float(mask.mean()), 4),
+                          "loss": round(float((lc + lm).detach()), 5), "mask_mean": round(float(mask.mean()), 4),
                           "d_triplane_absmax": float(tp_grad.abs().max()), "d_flow_absmax": float(f_grad.abs().max()),
                           "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}))
         del gen
