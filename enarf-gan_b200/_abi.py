@@ -53,6 +53,8 @@ _SIGNATURES = {
                                           _P, _P]),
     "enarf_triplane_sample_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                           c_int, _P, _P, _P]),
+    "enarf_triplane_sample_cl_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int64, c_int, c_int, _P, _P]),
+    "enarf_triplane_sample_cl_bwd": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int64, c_int, c_int, _P, _P, _P]),
 }
 EXPORTS = tuple(_SIGNATURES)
 

@@ -169,6 +169,17 @@ int enarf_triplane_sample_bwd(const float* grad_output, const float* input, cons
                               int H, int W, int Ho, int Wo, int interpolation, int padding, int align_corners,
                               float* grad_input, float* grad_grid, void* stream);
 
+/* Fast path of the same op for the reference's one real call shape (sampling.py:22-26: C = 32, bilinear): the planes
+ * are taken channels-last, feat_planes (N,3,H,W,32) = enarf_repack_planes of `input`; grid (N,points,3);
+ * output (N,32,points).  One texel is one 128-B line instead of 32 separate sectors. */
+int enarf_triplane_sample_cl_fwd(const float* feat_planes, const float* grid, int N, int H, int W, int64_t points,
+                                 int padding, int align_corners, float* output, void* stream);
+/* d_feat_planes (N,3,H,W,32) and grad_grid (N,points,3) are ADDED into (caller zero-initialises); either may be NULL.
+ * enarf_unpack_plane_grads turns d_feat_planes into the NCHW grad_input. */
+int enarf_triplane_sample_cl_bwd(const float* grad_output, const float* feat_planes, const float* grid, int N, int H,
+                                 int W, int64_t points, int padding, int align_corners, float* d_feat_planes,
+                                 float* grad_grid, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -112,11 +112,12 @@ def test_render_entire_img_is_chunk_invariant():
 @pytest.mark.parametrize("mode,padding,align", [("bilinear", "zeros", False), ("bilinear", "border", False),
                                                 ("bilinear", "reflection", True), ("bilinear", "zeros", True),
                                                 ("nearest", "zeros", False)])
-def test_triplane_sampler_matches_grid_sample(mode, padding, align):
+@pytest.mark.parametrize("C", [5, 32])      # 32 = channels-last fast path (bilinear), 5 = generic NCHW kernels
+def test_triplane_sampler_matches_grid_sample(mode, padding, align, C):
     """The stand-alone op (forward and both gradients) against three F.grid_sample calls."""
     from enarf_gan_b200.triplane_sampler import triplane_sampler
     torch.manual_seed(0)
-    N, C, H, W, n = 2, 5, 17, 23, 1000
+    N, C, H, W, n = 2, C, 17, 23, 1000
     inp = torch.randn(N, 3 * C, H, W, device="cuda", requires_grad=True)
     grid = (torch.rand(N, n, 1, 3, device="cuda") * 2.6 - 1.3).requires_grad_()
     out = triplane_sampler(inp, grid, mode, padding, align)
