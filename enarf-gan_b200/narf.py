@@ -202,6 +202,30 @@ class TriPlaneNARF(nn.Module):
             den, col, _ = ops.density_query(scene, position.to(torch.float32).contiguous())
         return den, col
 
+    def density_grid(self, pose_to_camera, center, voxel_size=0.003, model_input=None, chunk=1 << 24):
+        """The density volume ``create_mesh`` feeds to marching cubes (libraries/NARF/mesh_rendering.py:50-71):
+        (2/voxel_size + 1)^3 points on a regular grid around ``center`` (1,3,1), in the scaled camera frame, queried
+        through ``enarf_density_query``.  pose_to_camera (1,P,4,4) are part frames (``transform_pose`` applied, not yet
+        scaled; unlike the reference the caller's tensor is not modified in place).  The scene is built once, the
+        grid is generated on the device chunk by chunk and only the density volume is kept.
+        -> (S,S,S) fp32 on the device, S = 2*int(1/voxel_size)+1, indexed [x][y][z] like the reference's."""
+        cube = int(1 / voxel_size)
+        S = 2 * cube + 1
+        dev = pose_to_camera.device
+        scene, _, _ = self.build_scene(rendering._scaled(self, pose_to_camera), dict(model_input or {}))
+        bins = torch.arange(-cube, cube + 1, device=dev, dtype=torch.float32) / cube
+        c = center.to(dev, torch.float32).reshape(3)
+        out = torch.empty(S * S * S, device=dev)
+        with torch.no_grad():
+            for start in range(0, S * S * S, chunk):
+                idx = torch.arange(start, min(start + chunk, S * S * S), device=dev)
+                ix, iy, iz = torch.div(idx, S * S, rounding_mode="floor"), torch.div(idx, S, rounding_mode="floor") % S, idx % S
+                pts = torch.stack([bins[ix] + c[0], bins[iy] + c[1], bins[iz] + c[2]], dim=0)[None]
+                pts = (pts * self.coordinate_scale).contiguous()
+                den, _, _ = ops.density_query(scene, pts, want_color=False)
+                out[start:start + idx.numel()] = den.reshape(-1)
+        return out.reshape(S, S, S)
+
     # ---- NARFBase.forward / render_entire_img (libraries/NARF/base.py:26-63) --------------------------
     def forward(self, batchsize, sampled_img_coord, pose_to_camera, inv_intrinsics, z, z_rend, bone_length,
                 render_scale=1, Nc=64, Nf=128, return_intermediate=False, truncation_psi=1,

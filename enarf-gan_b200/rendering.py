@@ -143,7 +143,7 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
 def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Optional[torch.Tensor] = None,
                       render_size: int = 128, Nc: int = 64, Nf: int = 128, semantic_map: bool = False,
                       use_normalized_intrinsics: bool = False, no_grad: bool = True, model_input: Dict = {},
-                      bbox=None):
+                      bbox=None, ray_range=None):
     """Chunked full-image render with the reference's ``render_bs`` semantics (rendering.py:362-427): batch
     forced to 1, pixel centres (optionally bbox-cropped / normalised), chunks of ``model.config.render_bs``
     rays rendered independently and concatenated.  The scene (repacked planes, decoder weights) is built once."""
@@ -161,6 +161,8 @@ def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Option
     if use_normalized_intrinsics:
         x, y = x / render_size, y / render_size
     img_coord = torch.stack([x, y, torch.ones_like(x)], dim=0)[None, None]                # (1,1,3,n)
+    if ray_range is not None:          # this rank's block of the image's rays (render_entire_img_sharded)
+        img_coord = img_coord[..., ray_range[0]:ray_range[1]]
     pose1 = pose_to_camera[:1]
     mi = dict(model_input)
     for key in ("z", "z_rend", "bone_length", "tri_plane_feature"):
@@ -176,6 +178,8 @@ def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Option
             masks.append(m)
             disps.append(d)
         color, mask, disp = torch.cat(colors, dim=2), torch.cat(masks, dim=1), torch.cat(disps, dim=1)
+    if ray_range is not None:
+        return color[0], mask[0], disp[0]                                                 # (3,n_local), (n_local,) x2
     return color.reshape(3, height, width), mask.reshape(height, width), disp.reshape(height, width)
 
 
@@ -207,3 +211,46 @@ def global_near_far(pose_local, near0: float = NEAR_PLANE, far0: float = FAR_PLA
     near = torch.clamp_min(lo - sqrt3, near0)
     far = torch.clamp_min(hi + sqrt3, far0)
     return torch.cat([near, far])
+
+
+def shard_rays(n_rays: int, rank: int, world: int):
+    """Contiguous block of one image's rays rendered by ``rank`` when there are fewer samples than GPUs
+    (``render_entire_img`` has batch 1; SURVEY 8e "B < G")."""
+    return shard_samples(n_rays, rank, world)
+
+
+def gather_rays(local: torch.Tensor, n_rays: int, group=None):
+    """All-gather the per-rank ray blocks ``(..., n_local)`` into ``(..., n_rays)`` on every rank.  Blocks differ by
+    at most one ray, so they are padded to a common length for one ``all_gather`` and trimmed afterwards."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return local
+    world = dist.get_world_size(group)
+    longest = -(-n_rays // world)
+    pad = longest - local.shape[-1]
+    send = torch.nn.functional.pad(local, (0, pad)) if pad else local.contiguous()
+    parts = [torch.empty_like(send) for _ in range(world)]
+    dist.all_gather(parts, send.contiguous(), group=group)
+    out = []
+    for r, part in enumerate(parts):
+        lo, hi = shard_rays(n_rays, r, world)
+        out.append(part[..., :hi - lo])
+    return torch.cat(out, dim=-1)
+
+
+def render_entire_img_sharded(model, pose_to_camera, inv_intrinsics, render_size: int = 128, Nc: int = 64, Nf: int = 128,
+                              model_input: Dict = {}, group=None, **kw):
+    """``render_entire_img`` with the image's rays split across the ranks of ``group`` (every rank holds the model and
+    the planes -- replicated parameters, or ``model_input["tri_plane_feature"]`` broadcast by the caller): rank r renders
+    rays ``shard_rays(n, r, world)``, one all_gather per output assembles the image on every rank.  No gradient path:
+    training shards samples, not rays (``shard_samples``)."""
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+    rank = dist.get_rank(group) if world > 1 else 0
+    bbox = kw.get("bbox")
+    width, height = (bbox[2] - bbox[0], bbox[3] - bbox[1]) if bbox is not None else (render_size, render_size)
+    n = width * height
+    color, mask, disp = render_entire_img(model, pose_to_camera, inv_intrinsics, render_size=render_size, Nc=Nc, Nf=Nf,
+                                          model_input=model_input, ray_range=shard_rays(n, rank, world), **kw)
+    color, mask, disp = gather_rays(color, n, group), gather_rays(mask, n, group), gather_rays(disp, n, group)
+    return color.reshape(3, height, width), mask.reshape(height, width), disp.reshape(height, width)

@@ -149,3 +149,56 @@ def test_sampling_front_ends_match_oracle():
     assert rel(w.cpu() * valid, weight) < 1e-5
     f = sampling.sample_weighted_feature_v2(32, tp[:, :96].cuda(), masked.cuda(), w, valid.cuda())
     assert rel(f, feat) < 1e-5
+
+
+def test_density_grid_matches_oracle_query():
+    """The volume create_mesh feeds to marching cubes (mesh_rendering.py:50-71): grid layout, centre offset, coordinate
+    scale and chunking, against the oracle's point query on the same grid."""
+    import enarf_oracle as O
+    g, cfg, inp, tp, layers, z_rend = G.load("b1_s32")
+    gen = make_generator(cfg, tp, g).eval()
+    nerf = gen.nerf
+    sc = G.scene(cfg, inp, tp, layers, z_rend)
+    c = lambda k: inp[k].cuda()
+    pose, bl = nerf.transform_pose(c("pose_to_camera"), c("bone_length"))
+    z = S.make_latent(1, seed=cfg["seed"]).cuda()
+    mi = {"z": z[:, :512], "z_rend": z[:, 512:], "bone_length": bl, "tri_plane_feature": tp.cuda(), "truncation_psi": 1}
+    center = pose[:, 0, :3, 3:].clone()                              # (1,3,1): around the first part
+    before = pose.clone()
+    vol = nerf.density_grid(pose, center, voxel_size=0.1, model_input=mi, chunk=3000)
+    assert torch.equal(pose, before), "the caller's pose must not be scaled in place"
+    assert vol.shape == (21, 21, 21)
+    bins = torch.arange(-10, 11) / 10
+    pts = (torch.stack(torch.meshgrid(bins, bins, bins, indexing="ij")).reshape(1, 3, -1) + center.cpu()) * 3.0
+    with torch.no_grad():
+        den = sc.query(pts)[0]
+    assert den.abs().max() > 0
+    assert rel(vol.reshape(-1), den.reshape(-1)) < 1e-4
+
+
+def test_render_entire_img_ray_blocks_assemble_the_image():
+    """B < G sharding: the ray blocks ``shard_rays`` hands to 3 ranks, rendered one after the other here,
+    concatenate to the one-shot image (same scene; fine-pass draws differ per call -> Monte-Carlo tolerance, and the
+    rays outside every part are exactly zero in both)."""
+    from enarf_gan_b200 import rendering
+    g, cfg, inp, tp, layers, z_rend = G.load("b1_s32")
+    gen = make_generator(cfg, tp, g, render_bs=4096).eval()
+    nerf = gen.nerf
+    nerf.rng_mode = "philox"
+    z = S.make_latent(1, seed=cfg["seed"]).cuda()
+    c = lambda k: inp[k].cuda()
+    pose, bl = nerf.transform_pose(c("pose_to_camera"), c("bone_length"))
+    mi = {"z": z[:, :512], "z_rend": z[:, 512:], "bone_length": bl, "tri_plane_feature": tp.cuda(), "truncation_psi": 1}
+    full_c, full_m, _ = rendering.render_entire_img(nerf, pose, c("inv_intrinsics"), render_size=32, Nc=48, Nf=48,
+                                                    model_input=mi)
+    n, world = 32 * 32, 3
+    blocks = [rendering.render_entire_img(nerf, pose, c("inv_intrinsics"), render_size=32, Nc=48, Nf=48, model_input=mi,
+                                          ray_range=rendering.shard_rays(n, r, world)) for r in range(world)]
+    col = torch.cat([b[0] for b in blocks], dim=-1).reshape(3, 32, 32)
+    msk = torch.cat([b[1] for b in blocks], dim=-1).reshape(32, 32)
+    assert torch.equal(msk == 0, full_m == 0)
+    assert (msk - full_m).abs().mean() < 0.02 and (col - full_c).abs().mean() < 0.02
+    # single process: the sharded entry point is the plain one
+    one_c, one_m, _ = rendering.render_entire_img_sharded(nerf, pose, c("inv_intrinsics"), render_size=32, Nc=48, Nf=48,
+                                                          model_input=mi)
+    assert one_c.shape == (3, 32, 32) and torch.equal(one_m == 0, full_m == 0)

@@ -57,3 +57,29 @@ def test_global_near_far_matches_single_process(tmp_path):
     assert got[0]["range"] == (0, 3) and got[1]["range"] == (3, 5)
     for g in got:   # every rank holds the full-batch scalars, bit-identical to the oracle's
         assert torch.equal(g["nearfar"], torch.stack([near, far]).float())
+
+
+def _gather_worker(rank, world, port, n, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from enarf_gan_b200 import rendering
+        lo, hi = rendering.shard_rays(n, rank, world)
+        ray = torch.arange(lo, hi, dtype=torch.float32)
+        local = torch.stack([ray, ray * 2, ray * 3])                     # a (3, n_local) "colour" block
+        full = rendering.gather_rays(local, n)
+        mask = rendering.gather_rays(ray + 0.5, n)
+        torch.save({"full": full, "mask": mask}, os.path.join(out_dir, f"g{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ray_sharding_gathers_the_whole_image(tmp_path):
+    """B < G: one image's rays split over two ranks (uneven block sizes) and all-gathered back in ray order."""
+    n, world = 17 * 17, 2            # odd ray count: the blocks differ by one ray and are padded for the all_gather
+    mp.spawn(_gather_worker, args=(world, _free_port(), n, str(tmp_path)), nprocs=world, join=True)
+    ray = torch.arange(n, dtype=torch.float32)
+    for r in range(world):
+        got = torch.load(os.path.join(tmp_path, f"g{r}.pt"))
+        assert torch.equal(got["full"], torch.stack([ray, ray * 2, ray * 3]))
+        assert torch.equal(got["mask"], ray + 0.5)
