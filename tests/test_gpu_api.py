@@ -178,8 +178,8 @@ def test_density_grid_matches_oracle_query():
 
 def test_render_entire_img_ray_blocks_assemble_the_image():
     """B < G sharding: the ray blocks ``shard_rays`` hands to 3 ranks, rendered one after the other here,
-    concatenate to the one-shot image (same scene; fine-pass draws differ per call -> Monte-Carlo tolerance, and the
-    rays outside every part are exactly zero in both)."""
+    concatenate to the one-shot image (same scene; fine-pass draws differ per call -> Monte-Carlo tolerance; rays that
+    miss every part box are exactly zero in both)."""
     from enarf_gan_b200 import rendering
     g, cfg, inp, tp, layers, z_rend = G.load("b1_s32")
     gen = make_generator(cfg, tp, g, render_bs=4096).eval()
@@ -196,9 +196,12 @@ def test_render_entire_img_ray_blocks_assemble_the_image():
                                           ray_range=rendering.shard_rays(n, r, world)) for r in range(world)]
     col = torch.cat([b[0] for b in blocks], dim=-1).reshape(3, 32, 32)
     msk = torch.cat([b[1] for b in blocks], dim=-1).reshape(32, 32)
-    assert torch.equal(msk == 0, full_m == 0)
+    from enarf_gan_b200 import ops
+    img = rendering.pixel_grid(32, 32, 1, pose.device)
+    miss = ~ops.depth_range(img, c("inv_intrinsics"), rendering._scaled(nerf, pose))[3].reshape(32, 32)
+    assert miss.any() and (msk[miss] == 0).all() and (full_m[miss] == 0).all()
     assert (msk - full_m).abs().mean() < 0.02 and (col - full_c).abs().mean() < 0.02
     # single process: the sharded entry point is the plain one
     one_c, one_m, _ = rendering.render_entire_img_sharded(nerf, pose, c("inv_intrinsics"), render_size=32, Nc=48, Nf=48,
                                                           model_input=mi)
-    assert one_c.shape == (3, 32, 32) and torch.equal(one_m == 0, full_m == 0)
+    assert one_c.shape == (3, 32, 32) and (one_m[miss] == 0).all() and (one_m - full_m).abs().mean() < 0.02
