@@ -21,10 +21,22 @@ __global__ void __launch_bounds__(WARPS * 32) fine_sample_kernel(
             for (int j = lane; j < Nc; j += 32) cdf[j] = weights[(size_t)ray * Nc + j];
             __syncwarp();
             if (lane == 0) {
-                float c = cdf[0];
-                for (int j = 1; j < Nc; ++j) {
-                    c = cadd(c, cdf[j]);
-                    cdf[j] = c;
+                // sequential fp32 prefix sum (the oracle's contract), 16 elements at a time: the chunk is read into
+                // registers with independent loads, summed in registers (one dependent add per element) and written
+                // back, instead of one shared-memory round trip per element
+                float c = 0.f;
+                for (int j0 = 0; j0 < Nc; j0 += 16) {
+                    float w[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) w[i] = (j0 + i < Nc) ? cdf[j0 + i] : 0.f;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        c = (j0 + i == 0) ? w[0] : cadd(c, w[i]);
+                        w[i] = c;
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (j0 + i < Nc) cdf[j0 + i] = w[i];
                 }
             }
             __syncwarp();
@@ -118,7 +130,7 @@ extern "C" int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, in
     int Nf2 = 1;
     while (Nf2 < Nf) Nf2 <<= 1;
     const size_t smem = (size_t)WARPS * (Nc + Nf2) * sizeof(float);
-    const int grid = min((R + WARPS - 1) / WARPS, 8 * enarf_sm_count());
+    const int grid = min((R + WARPS - 1) / WARPS, 16 * enarf_sm_count());
     fine_sample_kernel<<<grid, WARPS * 32, smem, (cudaStream_t)stream>>>(weights, R, Nc, Nf, Nf2, mode, idx, jitter, seed,
                                                                          ray_id_offset, bins_out, idx_out);
     ENARF_CHECK_LAUNCH("enarf_fine_sample");
