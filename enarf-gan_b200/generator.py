@@ -155,20 +155,19 @@ class DSONARFGenerator(nn.Module):
     @staticmethod
     def pose_encoding(pose: torch.Tensor):
         """(B,num_bone,4,4) -> (B,(num_bone-1)*9): every joint rotation relative to the root's."""
-        rot = pose[:, 1:, :3, :3]
-        root_rot = pose[:, :1, :3, :3]
-        encoded = torch.matmul(root_rot.permute(0, 1, 3, 2), rot)
-        return encoded.reshape(encoded.shape[0], -1)
+        R = pose[..., :3, :3]
+        relative = R[:, :1].transpose(-1, -2) @ R[:, 1:]            # root^T . joint
+        return relative.flatten(1)
 
     def get_latents(self, frame_time: torch.Tensor, pose_to_camera: torch.Tensor):
-        zs = []
-        if self.time_conditional:
-            zs.append(self.positional_encoding(frame_time, num_frequency=10))
-        if self.pose_conditional:
-            zs.append(self.pose_encoding(pose_to_camera))
-        assert len(zs) > 0
-        z = torch.cat(zs, dim=1)
-        return z, z
+        """(z for the tri-plane / flow head, z for the decoder modulation): the same conditioning vector twice
+        (models/generator.py:204-217)."""
+        parts = ([self.positional_encoding(frame_time, num_frequency=10)] if self.time_conditional else []) \
+            + ([self.pose_encoding(pose_to_camera)] if self.pose_conditional else [])
+        if not parts:
+            raise AssertionError("DSONARFGenerator needs time_conditional or pose_conditional")
+        latent = torch.cat(parts, dim=1)
+        return latent, latent
 
     def forward(self, pose_to_camera, camera_pose, mask, frame_time, bone_length, inv_intrinsics,
                 background: Optional[float] = None):
