@@ -246,9 +246,10 @@ class TriPlaneNARF(nn.Module):
                           no_grad=True, truncation_psi=1, bbox=None):
         model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
         pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
-        if self.deformation_field:      # same hoisting as NARF/base.py:59-60, in the hand-off layout
-            model_input["planes"] = self.warped_planes(self.compute_flow(z[:1], bone_length[:1], truncation_psi))
-        else:
-            model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
+        with torch.set_grad_enabled(not no_grad):
+            if self.deformation_field:      # same hoisting as NARF/base.py:59-60, in the hand-off layout
+                model_input["planes"] = self.warped_planes(self.compute_flow(z[:1], bone_length[:1], truncation_psi))
+            else:
+                model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
         return rendering.render_entire_img(self, pose_to_camera, inv_intrinsics, camera_pose, render_size, Nc, Nf,
                                            semantic_map, use_normalized_intrinsics, no_grad, model_input, bbox=bbox)

@@ -206,3 +206,27 @@ def test_dso_step_gradients(name, plane_dtype, tol):
         conv = gen.nerf.mlp.layers[i].conv
         assert rel(conv.weight.grad[0, :, :, 0], L["weight"].grad) < max(tol, 1e-3), f"decoder weight {i}"
         assert rel(conv.modulation.weight.grad, L["mod_weight"].grad) < max(tol, 1e-3), f"modulation weight {i}"
+
+
+def test_dso_render_entire_img_agrees_with_sparse_forward():
+    """DSONARFGenerator.render_entire_img (chunked, batch forced to 1, planes warped once) against forward() on all
+    pixels of the same frame: same scene, independent fine-pass draws -> Monte-Carlo tolerance; rays that miss every part
+    are exactly zero / background in both."""
+    g, cfg, inp, canon, flow, layers = G.load_dso("dso_b1_s64")
+    size = cfg["size"]
+    gen = _dso_generator(dict(cfg, ray_bs=size * size), canon, flow, g).eval()
+    gen.nerf.rng_mode = "philox"
+    gen.nerf.config["render_bs"] = 1000                               # 5 chunks, the last one ragged
+    c = lambda k: inp[k].cuda()
+    t = torch.from_numpy(g["frame_time"]).cuda()
+    ray_idx = torch.arange(size * size, device="cuda")[None]
+    gen.ray_sampler = lambda mask, ray_bs: (ray_idx, G.dso_image_coord(ray_idx.cpu(), size)[:, None].cuda())
+    with torch.no_grad():
+        color, mask, _ = gen(c("pose_to_camera"), None, None, t, c("bone_length"), c("inv_intrinsics"), background=0.0)
+        img_c, img_m, img_d = gen.render_entire_img(c("pose_to_camera"), c("inv_intrinsics"), t, c("bone_length"),
+                                                    render_size=size)
+    assert img_c.shape == (3, size, size) and img_m.shape == (size, size) and img_d.shape == (size, size)
+    m = mask.reshape(size, size)
+    assert img_m.max() > 0.5
+    assert (img_m - m).abs().mean() < 0.02 and (img_c - color.reshape(3, size, size)).abs().mean() < 0.02
+    assert not gen.nerf.tri_plane.requires_grad or img_c.grad_fn is None        # no_grad=True: nothing tracked
