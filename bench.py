@@ -154,7 +154,8 @@ def step_device(w, step_idx, timer=None, world=None):
     color, mask, disp, fw, fd, pts, feat, pairs = timed("fine_fwd", lambda: ops._render_fine_fwd(
         scene, dmin, dmax, direction, bins, want_points=True, want_feat=True, want_pairs=True))
     d_tp = torch.empty_like(w["tri_plane"])     # as ops.RenderFine.backward: feature channels are stored by unpack
-    d_tp[:, 96:].zero_()
+    for b in range(B):                          # per sample: contiguous slices -> vectorised fills
+        d_tp[b, 96:].zero_()
     d_feat = torch.zeros(B, 3, scene.H, scene.W, 32, device=dev)
     dw = [torch.zeros_like(t) for t in scene.w]
     db = [torch.zeros_like(t) for t in scene.b]
