@@ -16,7 +16,14 @@ __global__ void __launch_bounds__(256) k(float* buf, uint32_t lines, int iters) 
         const float v = (float)i;
         if (MODE == 0) asm volatile("red.global.add.v4.f32 [%0], {%1,%1,%1,%1};" ::"l"(p), "f"(v));
         else if (MODE == 1) asm volatile("st.global.v4.f32 [%0], {%1,%1,%1,%1};" ::"l"(p), "f"(v));
-        else asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v));
+        else if (MODE == 2) asm volatile("red.global.add.f32 [%0], %1;" ::"l"(p), "f"(v));
+        else {
+            // MODE 3: every lane its own pseudo-random 4-B word (the probability-plane reductions of the backward:
+            // one lane per texel, a warp-level instruction touches up to 32 different sectors)
+            uint32_t s2 = (st ^ (threadIdx.x * 0x9E3779B9u)) * 1664525u + 1013904223u;
+            float* q = buf + (size_t)((s2 >> 3) % (lines * 32u));
+            asm volatile("red.global.add.f32 [%0], %1;" ::"l"(q), "f"(v));
+        }
     }
 }
 int main() {
@@ -26,22 +33,23 @@ int main() {
         cudaMalloc(&buf, (size_t)lines * 128);
         cudaMemset(buf, 0, (size_t)lines * 128);
         const int iters = 256, grid = 148 * 8;
-        for (int mode = 0; mode < 3; ++mode) {
+        for (int mode = 0; mode < 4; ++mode) {
             cudaEvent_t a, b;
             cudaEventCreate(&a); cudaEventCreate(&b);
             for (int rep = 0; rep < 2; ++rep) {
                 cudaEventRecord(a);
                 if (mode == 0) k<0><<<grid, 256>>>(buf, lines, iters);
                 else if (mode == 1) k<1><<<grid, 256>>>(buf, lines, iters);
-                else k<2><<<grid, 256>>>(buf, lines, iters);
+                else if (mode == 2) k<2><<<grid, 256>>>(buf, lines, iters);
+                else k<3><<<grid, 256>>>(buf, lines, iters);
                 cudaEventRecord(b);
                 cudaEventSynchronize(b);
             }
             float ms;
             cudaEventElapsedTime(&ms, a, b);
-            const double bytes = (double)grid * 256 * iters * (mode == 2 ? 4 : 16);
+            const double bytes = (double)grid * 256 * iters * (mode >= 2 ? 4 : 16);
             printf("%4zu MB buffer  %-18s %8.3f ms  %7.1f GB/s  (%.2f G lane-ops/s)\n", mb,
-                   mode == 0 ? "red.add.v4.f32" : mode == 1 ? "st.v4.f32" : "red.add.f32 (4 B)", ms, bytes / ms / 1e6,
+                   mode == 0 ? "red.add.v4.f32" : mode == 1 ? "st.v4.f32" : mode == 2 ? "red.add.f32 (4 B)" : "red.add.f32 scattered", ms, bytes / ms / 1e6,
                    (double)grid * 256 * iters / ms / 1e6);
         }
         cudaFree(buf);
