@@ -271,6 +271,45 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     return out
 
 
+def _fine_forward(ctx, scene, dmin, dmax, direction, bins):
+    """Forward of both autograd Functions: run the fused pass with the checkpoints a backward wants and stash them."""
+    pairs_on = SAVE_FEATURES and PAIR_CKPT
+    out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
+                           want_pairs=pairs_on)
+    ctx.scene = scene
+    saved = [dmin, dmax, direction, bins, out[5]]
+    if SAVE_FEATURES:
+        saved.append(out[6])
+    if pairs_on:
+        saved.extend(out[7].tensors())
+    ctx.has_feat, ctx.has_pairs = SAVE_FEATURES, pairs_on
+    ctx.save_for_backward(*saved)
+    out = out[:6]
+    ctx.mark_non_differentiable(out[4], out[5])
+    return out
+
+
+def _fine_backward(ctx, grads, d_feat, d_prob, d_prob_stride):
+    """Backward of both: launches enarf_render_fine_bwd into the caller's zero-initialised plane-gradient buffers and
+    returns (dW1, dW2, dW3, db1, db2, db3) shaped like the decoder tensors the forward was given."""
+    scene = ctx.scene
+    dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
+    feat = rest.pop(0) if ctx.has_feat else None
+    pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
+    _, n, Nf = bins.shape
+    g = [None if t is None else t.contiguous().float() for t in grads]
+    dw = [torch.zeros_like(w) for w in scene.w]
+    db = [torch.zeros_like(b) for b in scene.b]
+    check(lib().enarf_render_fine_bwd(
+        scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True),
+        pairs.ref if pairs else None, n, Nf,
+        ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
+        ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_prob_stride,
+        ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+    return (dw[0], dw[1], dw[2], db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)),
+            db[2].reshape(ctx_shape(scene, 2)))
+
+
 class RenderFine(torch.autograd.Function):
     """Fused fine pass.  Differentiable inputs: tri_plane (NCHW, features and probabilities), the three
     W_eff and the three biases; everything else (pose, rays, bins) carries no gradient, as in the
@@ -278,55 +317,27 @@ class RenderFine(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
-        pairs_on = SAVE_FEATURES and PAIR_CKPT
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
-                               want_pairs=pairs_on)
-        ctx.scene = scene
-        saved = [dmin, dmax, direction, bins, out[5]]
-        if SAVE_FEATURES:
-            saved.append(out[6])
-        if pairs_on:
-            saved.extend(out[7].tensors())
-        ctx.has_feat, ctx.has_pairs = SAVE_FEATURES, pairs_on
-        ctx.save_for_backward(*saved)
-        out = out[:6]
         ctx.tp_shape = tri_plane.shape
-        ctx.mark_non_differentiable(out[4], out[5])
-        return out
+        return _fine_forward(ctx, scene, dmin, dmax, direction, bins)
 
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
         scene = ctx.scene
-        dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
-        feat = rest.pop(0) if ctx.has_feat else None
-        pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
-        B, n, Nf = bins.shape
-        dev = bins.device
-        c = lambda g: None if g is None else g.contiguous().float()
+        B, dev = scene.B, ctx.saved_tensors[0].device
         need_tp = ctx.needs_input_grad[5]
         # the feature channels of d_tp are overwritten by unpack_plane_grads: only the probability channels
         # (scattered into directly) and the channels-last scratch need zero-filling
         d_tp = torch.empty(ctx.tp_shape, device=dev) if need_tp else torch.zeros(ctx.tp_shape, device=dev)
         d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
-        d_prob = d_tp[:, FEAT_DIM * 3:]
         if need_tp:
             # per sample: each slice is contiguous, so the fill is the vectorised one (the strided view of the whole
             # batch falls back to torch's generic element-wise fill: 78 us instead of ~25 us for 151 MB)
             for b in range(d_tp.shape[0]):
                 d_tp[b, FEAT_DIM * 3:].zero_()
-        dw = [torch.zeros_like(w) for w in scene.w]
-        db = [torch.zeros_like(b) for b in scene.b]
-        g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
-        check(lib().enarf_render_fine_bwd(
-            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True),
-            pairs.ref if pairs else None, n, Nf,
-            ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
-            ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_tp.stride(0),
-            ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+        dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_tp[:, FEAT_DIM * 3:], d_tp.stride(0))
         if need_tp:
             unpack_plane_grads(d_feat, d_tp, accumulate=False)
-        return (None, None, None, None, None, d_tp if need_tp else None, dw[0], dw[1], dw[2],
-                db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
+        return (None, None, None, None, None, d_tp if need_tp else None) + dec
 
 
 class RenderFinePlanes(torch.autograd.Function):
@@ -336,46 +347,19 @@ class RenderFinePlanes(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, scene, dmin, dmax, direction, bins, feat_planes, prob_planes, w1, w2, w3, b1, b2, b3):
-        pairs_on = SAVE_FEATURES and PAIR_CKPT
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
-                               want_pairs=pairs_on)
-        ctx.scene = scene
-        saved = [dmin, dmax, direction, bins, out[5]]
-        if SAVE_FEATURES:
-            saved.append(out[6])
-        if pairs_on:
-            saved.extend(out[7].tensors())
-        ctx.has_feat, ctx.has_pairs = SAVE_FEATURES, pairs_on
-        ctx.save_for_backward(*saved)
         ctx.prob_shape = prob_planes.shape
-        out = out[:6]
-        ctx.mark_non_differentiable(out[4], out[5])
-        return out
+        return _fine_forward(ctx, scene, dmin, dmax, direction, bins)
 
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
         scene = ctx.scene
-        dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
-        feat = rest.pop(0) if ctx.has_feat else None
-        pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
-        B, n, Nf = bins.shape
-        dev = bins.device
-        c = lambda g: None if g is None else g.contiguous().float()
-        d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
+        dev = ctx.saved_tensors[0].device
+        d_feat = torch.zeros(scene.B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
         d_prob = torch.zeros(ctx.prob_shape, device=dev)
         stride = 0 if ctx.prob_shape[0] == 1 else d_prob.stride(0)
-        dw = [torch.zeros_like(w) for w in scene.w]
-        db = [torch.zeros_like(b) for b in scene.b]
-        g = [c(g_color), c(g_mask), c(g_disp), c(g_fw)]
-        check(lib().enarf_render_fine_bwd(
-            scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), ptr(pts), ptr(feat, allow_none=True),
-            pairs.ref if pairs else None, n, Nf,
-            ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
-            ptr(g[3], allow_none=True), ptr(d_feat), ptr(d_prob), stride,
-            ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+        dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_prob, stride)
         return (None, None, None, None, None, d_feat if ctx.needs_input_grad[5] else None,
-                d_prob if ctx.needs_input_grad[6] else None, dw[0], dw[1], dw[2],
-                db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)), db[2].reshape(ctx_shape(scene, 2)))
+                d_prob if ctx.needs_input_grad[6] else None) + dec
 
 
 def ctx_shape(scene, i):
