@@ -196,11 +196,11 @@ __device__ __forceinline__ void wgrad_flush(WGrad& wg, const Maps& m, float* db3
 
 // forward layer on the tensor pipe: dst[o][pt] = lrelu(sum_k src[k][pt] W[o][k] + bias[o]) * sqrt2
 // warp tile: points 32*pb .. +31, outs 16*ob .. +15
-template <int K>
+template <int K, bool FAST>
 __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm, int ws, const float* bias, float* dst,
                                               const Maps& m) {
     float acc[2][2][4];
-    gemm_pts_mma<K, 2, false>(src, Wm, ws, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
+    gemm_pts_mma<K, 2, false, FAST>(src, Wm, ws, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
     for (int nt = 0; nt < 2; ++nt) {
         const int col = 16 * m.ob + 8 * nt + 2 * m.t;
@@ -298,6 +298,11 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
 
 template <typename T>
 __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
+    // bf16 feature planes (parity bar 1e-2): single-pass TF32 GEMMs instead of the error-compensated 3xTF32
+    // single-pass TF32 (mma_smem.cuh FAST) is available but off: in bf16-plane mode it made the DSO step 9 % faster and
+    // put the plane gradient at 1.4e-2 of its max-norm (activation kinks move), over the 1e-2 bar of that mode
+    constexpr bool FAST = false;
+    constexpr bool FASTG = false;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BwdSmem& s = *reinterpret_cast<BwdSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -471,10 +476,10 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             }
             // with the checkpoint, X of this chunk was stored during the previous chunk's scatter (or before the loop)
             PHASE(3);   // records + X load
-            if (tile_on) decoder_layer<FEAT>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
+            if (tile_on) decoder_layer<FEAT, FAST>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
             PHASE(4);   // L1
-            if (tile_on) decoder_layer<HID>(s.A1, s.dec.w2, W2S, s.dec.b2, s.A2, m);
+            if (tile_on) decoder_layer<HID, FAST>(s.A1, s.dec.w2, W2S, s.dec.b2, s.A2, m);
             __syncthreads();
             PHASE(5);   // L2
             if (8 * warp < cend) {   // head forward + backward: four lanes per point, lane c owns output c
@@ -533,12 +538,12 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             __syncthreads();
             PHASE(7);   // G2 pass
             // dW2 += G2^T A1 over the chunk's points: warp tile rows (o) 16 wr.., cols (i) 8 TN2 wc..
-            wgrad_mma<TN2>(s.A2, s.A1, 16 * m.wr, 8 * TN2 * m.wc, cend, m.g, m.t, wg.w2);
+            wgrad_mma<TN2, FASTG>(s.A2, s.A1, 16 * m.wr, 8 * TN2 * m.wc, cend, m.g, m.t, wg.w2);
             __syncthreads();
             PHASE(8);   // dW2
             if (tile_on) {   // G1 = (G2 W2) * act'(a1), in place over A1; db1 partial sums
                 float acc[2][2][4];
-                gemm_pts_mma<HID, 2, true>(s.A2, s.dec.w2, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
+                gemm_pts_mma<HID, 2, true, FASTG>(s.A2, s.dec.w2, W2S, 32 * m.pb, 16 * m.ob, m.g, m.t, acc);
 #pragma unroll
                 for (int nt = 0; nt < 2; ++nt) {
                     const int col = 16 * m.ob + 8 * nt + 2 * m.t;
@@ -559,11 +564,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             __syncthreads();
             PHASE(9);   // G1
             // dW1 += G1^T X: warp tile rows (o) 16 wr.., cols (c) 8 TN1 wc..
-            wgrad_mma<TN1>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
+            wgrad_mma<TN1, FASTG>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
             // no barrier: dX goes to the rows of A2 (G2 is dead after the G1 phase), so X and G1 are only read here
             if (tile_on) {   // dX = G1 W1 -> A2 rows 0..31: warp tile points 32 pb.., channels 8 ob..
                 float acc[2][1][4];
-                gemm_pts_mma<HID, 1, true>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
+                gemm_pts_mma<HID, 1, true, FASTG>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
                 const int col = 8 * m.ob + 2 * m.t;
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {

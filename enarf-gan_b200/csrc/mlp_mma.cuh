@@ -55,16 +55,27 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
         : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// FAST (bf16-plane modes, parity bar 1e-2): one TF32 product instead of three -- hi is x rounded to nearest TF32
+// (unbiased, 2^-11 relative, below the 2^-9 of the bf16 planes themselves) and lo is never formed.
+template <bool FAST = false>
 __device__ __forceinline__ void split_tf32(float x, uint32_t& hi, uint32_t& lo) {
-    hi = __float_as_uint(x) & 0xffffe000u;
-    lo = __float_as_uint(x - __uint_as_float(hi));
+    if (FAST) {
+        asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(hi) : "f"(x));
+        lo = 0u;
+    } else {
+        hi = __float_as_uint(x) & 0xffffe000u;
+        lo = __float_as_uint(x - __uint_as_float(hi));
+    }
 }
 
 // One k-block of one 16-row tile against one n-tile: main += hi*hi, small += lo*hi + hi*lo
+template <bool FAST = false>
 __device__ __forceinline__ void mma3(float (&main)[4], float (&small)[4], const uint32_t (&ah)[4], const uint32_t (&al)[4],
                                      uint32_t bh0, uint32_t bh1, uint32_t bl0, uint32_t bl1) {
-    mma_tf32(small, al, bh0, bh1);
-    mma_tf32(small, ah, bl0, bl1);
+    if (!FAST) {
+        mma_tf32(small, al, bh0, bh1);
+        mma_tf32(small, ah, bl0, bl1);
+    }
     mma_tf32(main, ah, bh0, bh1);
 }
 
@@ -74,6 +85,7 @@ __device__ __forceinline__ void mma3(float (&main)[4], float (&small)[4], const 
 // o3[mt][2] = (point 16mt+g+8, channel 2t)   o3[mt][3] = (point 16mt+g+8, channel 2t+1);  channels >= 4 are padding.
 // A1: at least 32 * A1S floats of the warp's own shared memory, may alias X.
 #define A1S 64
+template <bool FAST = false>
 __device__ __forceinline__ void decode32_mma(const float* X, float* A1, const DecoderMma& d, int lane, float (&o3)[2][4]) {
     const int g = lane >> 2, t = lane & 3;
     float acc1[2][8][4];
@@ -93,21 +105,23 @@ __device__ __forceinline__ void decode32_mma(const float* X, float* A1, const De
             const int col = xs_col(g, 8 * j + 2 * t);   // rows g, g+8, g+16, g+24 share (row & 3)
             const float2 v0 = *reinterpret_cast<const float2*>(X + (16 * mt + g) * XS + col);
             const float2 v1 = *reinterpret_cast<const float2*>(X + (16 * mt + g + 8) * XS + col);
-            split_tf32(v0.x, ah[mt][0], al[mt][0]);
-            split_tf32(v1.x, ah[mt][1], al[mt][1]);
-            split_tf32(v0.y, ah[mt][2], al[mt][2]);
-            split_tf32(v1.y, ah[mt][3], al[mt][3]);
+            split_tf32<FAST>(v0.x, ah[mt][0], al[mt][0]);
+            split_tf32<FAST>(v1.x, ah[mt][1], al[mt][1]);
+            split_tf32<FAST>(v0.y, ah[mt][2], al[mt][2]);
+            split_tf32<FAST>(v1.y, ah[mt][3], al[mt][3]);
         }
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
             const float2 w = *reinterpret_cast<const float2*>(d.w1 + (8 * nt + g) * W1M + 8 * j + 2 * t);
             uint32_t bh0, bl0, bh1, bl1;
-            split_tf32(w.x, bh0, bl0);
-            split_tf32(w.y, bh1, bl1);
+            split_tf32<FAST>(w.x, bh0, bl0);
+            split_tf32<FAST>(w.y, bh1, bl1);
+            if (!FAST) {
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], al[mt], bh0, bh1);
+                for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], al[mt], bh0, bh1);
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], ah[mt], bl0, bl1);
+                for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], ah[mt], bl0, bl1);
+            }
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) mma_tf32(acc1[mt][nt], ah[mt], bh0, bh1);
         }
@@ -155,21 +169,23 @@ __device__ __forceinline__ void decode32_mma(const float* X, float* A1, const De
             const int col = xs_col(g, 8 * j + 2 * t);
             const float2 v0 = *reinterpret_cast<const float2*>(A1 + (16 * mt + g) * A1S + col);
             const float2 v1 = *reinterpret_cast<const float2*>(A1 + (16 * mt + g + 8) * A1S + col);
-            split_tf32(v0.x, ah[mt][0], al[mt][0]);
-            split_tf32(v1.x, ah[mt][1], al[mt][1]);
-            split_tf32(v0.y, ah[mt][2], al[mt][2]);
-            split_tf32(v1.y, ah[mt][3], al[mt][3]);
+            split_tf32<FAST>(v0.x, ah[mt][0], al[mt][0]);
+            split_tf32<FAST>(v1.x, ah[mt][1], al[mt][1]);
+            split_tf32<FAST>(v0.y, ah[mt][2], al[mt][2]);
+            split_tf32<FAST>(v1.y, ah[mt][3], al[mt][3]);
         }
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
             const float2 w = *reinterpret_cast<const float2*>(d.w2 + (8 * nt + g) * W2M + 8 * j + 2 * t);
             uint32_t bh0, bl0, bh1, bl1;
-            split_tf32(w.x, bh0, bl0);
-            split_tf32(w.y, bh1, bl1);
+            split_tf32<FAST>(w.x, bh0, bl0);
+            split_tf32<FAST>(w.y, bh1, bl1);
+            if (!FAST) {
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], al[mt], bh0, bh1);
+                for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], al[mt], bh0, bh1);
 #pragma unroll
-            for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], ah[mt], bl0, bl1);
+                for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], ah[mt], bl0, bl1);
+            }
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt) mma_tf32(acc2[mt][nt], ah[mt], bh0, bh1);
         }
@@ -186,16 +202,16 @@ __device__ __forceinline__ void decode32_mma(const float* X, float* A1, const De
         const float2 b = *reinterpret_cast<const float2*>(d.b2 + 8 * nt + 2 * t);
         const float2 w3 = *reinterpret_cast<const float2*>(d.w3 + g * W2M + 8 * nt + 2 * t);
         uint32_t bh0, bl0, bh1, bl1;
-        split_tf32(w3.x, bh0, bl0);
-        split_tf32(w3.y, bh1, bl1);
+        split_tf32<FAST>(w3.x, bh0, bl0);
+        split_tf32<FAST>(w3.y, bh1, bl1);
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
             uint32_t ah[4], al[4];
-            split_tf32(lrelu_s2(acc2[mt][nt][0] + b.x), ah[0], al[0]);
-            split_tf32(lrelu_s2(acc2[mt][nt][2] + b.x), ah[1], al[1]);
-            split_tf32(lrelu_s2(acc2[mt][nt][1] + b.y), ah[2], al[2]);
-            split_tf32(lrelu_s2(acc2[mt][nt][3] + b.y), ah[3], al[3]);
-            mma3(m3[mt], s3[mt], ah, al, bh0, bh1, bl0, bl1);
+            split_tf32<FAST>(lrelu_s2(acc2[mt][nt][0] + b.x), ah[0], al[0]);
+            split_tf32<FAST>(lrelu_s2(acc2[mt][nt][2] + b.x), ah[1], al[1]);
+            split_tf32<FAST>(lrelu_s2(acc2[mt][nt][1] + b.y), ah[2], al[2]);
+            split_tf32<FAST>(lrelu_s2(acc2[mt][nt][3] + b.y), ah[3], al[3]);
+            mma3<FAST>(m3[mt], s3[mt], ah, al, bh0, bh1, bl0, bl1);
         }
     }
     const float2 b3 = *reinterpret_cast<const float2*>(d.b3 + 2 * t);

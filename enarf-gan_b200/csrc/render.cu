@@ -148,7 +148,10 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                                *reinterpret_cast<const float4*>(my.X + q * XSW + xs_col(q, 4 * (lane & 7))));
                 }
                 float o3[2][4];
-                decode32_mma(my.X, my.X, s.dec, lane, o3);   // layer-1 activations overwrite the slab (X + records)
+                // bf16 planes (parity bar 1e-2): the coarse pass only shapes the sampling distribution and carries no
+                // gradient, so its decoder runs single-pass TF32; the fine pass keeps 3xTF32 (with single-pass TF32
+                // there the DSO step's plane gradient sat at 1.4e-2 of its max-norm: activation kinks)
+                decode32_mma<(sizeof(T) == 2 && MODE == MODE_COARSE)>(my.X, my.X, s.dec, lane, o3);   // layer-1 activations overwrite the slab (X + records)
                 __syncwarp();   // every lane is done reading X before the next chunk's gather overwrites it
                 // rgb = tanh(.) (triplane_nerf.py:46); density = relu(.) * 10 (narf.py:274); every layer incl. the
                 // last is conv + bias -> LeakyReLU(0.2) * sqrt2 (custom_stylegan2/net.py:317-318).
