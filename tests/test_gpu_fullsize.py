@@ -139,3 +139,34 @@ def test_backward_is_positively_homogeneous():
     assert g1[0].abs().max().item() > 0
     # the feature-plane gradient only touches texels, the probability-plane gradient only the 3*P part channels
     assert torch.isfinite(g1[0]).all()
+
+
+def test_config4_size_bf16_planes_properties():
+    """BASELINE configs[3] per-sample size: 512 x 512 rays, 96 + 96 samples per ray, bf16 feature planes (B = 2 here to
+    bound the run time; the full B = 4 step is scripts/config4_dso.py).  Same size-independent properties, plus the
+    bf16 render against the fp32 render of the same scene within the mode's 1e-2 bar."""
+    from enarf_gan_b200 import hostmath, ops, rendering, synthetic as S
+    size, ns, B, seed = 512, 96, 2, 1238
+    dev = torch.device("cuda:0")
+    inp = S.make_inputs(B, size, seed=seed)
+    tp = S.make_triplane(B, seed=seed).to(dev)
+    s32 = hostmath.random_scene(inp, tp, seed=seed, device=dev)
+    dec = [(w, b) for w, b in zip(s32.w, s32.b)]
+    s16 = ops.SceneBuffers(s32.pose, s32.cscale, s32.canon_pose, tp, dec, plane_dtype=torch.bfloat16)
+    img = rendering.pixel_grid(size, size, B, dev)
+    invK = inp["inv_intrinsics"].to(dev)
+    # same fine samples for both precisions: take the fp32 coarse pass's bins
+    o32 = rendering.render_rays(s32, img, invK, ns, ns, rng="philox", seed=5, return_intermediate=True)
+    bins, dmin, dmax, direction = o32["bins"], o32["depth_min"], o32["depth_max"], o32["direction"]
+    c16, m16, d16, fw16, fd16 = ops.render_fine(s16, dmin, dmax, direction, bins)[:5]
+    assert fw16.shape == (B, size * size, ns - 1)
+    assert (bins[..., 1:] >= bins[..., :-1]).all() and (bins >= 0).all() and (bins <= 1).all()
+    assert torch.isfinite(c16).all() and torch.isfinite(d16).all()
+    assert (fw16.sum(-1) - m16).abs().max().item() < 1e-5
+    assert m16.min().item() >= -1e-4 and m16.max().item() <= 1 + 1e-5
+    # one-ulp depth inversions give a few weights of about -1e-5 (see above): |sum w c| may exceed sum w by twice that
+    assert (c16.abs() <= m16[:, None] + 1e-4).all()
+    assert torch.equal(fd16, o32["fine_depth"])                      # depths do not depend on the plane dtype
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max()).item()
+    assert rel(m16, o32["mask"]) < 1e-2 and rel(c16, o32["color"]) < 1e-2 and rel(fw16, o32["fine_weights"]) < 1e-2
+    assert o32["mask"].max().item() > 0.5
