@@ -5,8 +5,9 @@
 
 One "step" = one forward+backward pass of the hot path over one synthetic batch: plane repack -> near/far ->
 depth range -> fused coarse pass -> fine sampling -> fused fine pass -> fused backward -> gradient unpack.
-Workload (config.workload): BASELINE.json configs[1]/[2] shapes -- 128x128 rays per sample, 48+48 samples per
-ray, P=24 parts, fp32, batch 8 per GPU (weak scaling: global batch 8*N; N=4 is configs[2]'s batch 32).
+Workload (config.workload): BASELINE.json configs[2] -- 128x128 rays per sample, 48+48 samples per ray, P=24
+parts, fp32, GLOBAL batch 32 sample-sharded over the N ranks (32/N samples per GPU: strong scaling, the curve the
+metric is quoted on).  ``--batch b`` instead gives every GPU b samples (weak scaling, the round-1 curve).
 Prints ONE JSON line on rank 0 (see the driver contract in the task statement).
 """
 import argparse
@@ -23,6 +24,7 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 SIZE, NC, NF, PARTS = 128, 48, 48, 24
+GLOBAL_BATCH = 32   # BASELINE.json configs[2]
 SEED = 1236  # 1234 + config index 2
 
 
@@ -32,8 +34,11 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=8, help="samples per GPU")
+    ap.add_argument("--batch", type=int, default=None,
+                    help="samples per GPU (weak scaling); default: configs[2]'s global batch 32 split over the ranks")
+    ap.add_argument("--global-batch", type=int, default=GLOBAL_BATCH)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's eager path on this GPU")
     return ap.parse_args()
 
 
@@ -85,18 +90,30 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------------
 # workload
 # ----------------------------------------------------------------------------------------------------
-def build_workload(rank, B, device):
+def local_batch(args, rank, world):
+    """(first sample, samples) of this rank: configs[2]'s fixed global batch split over the ranks (strong scaling),
+    or ``--batch`` samples on every rank (weak scaling)."""
+    if args.batch is not None:
+        return rank * args.batch, args.batch
+    from enarf_gan_b200.rendering import shard_samples
+    lo, hi = shard_samples(args.global_batch, rank, world)
+    return lo, hi - lo
+
+
+def build_workload(first, B, device):
     """Synthetic batch resident in HBM: part frames, tri-planes (NCHW, as the reference produces them),
-    per-sample decoder weights, rays, and fixed upstream gradients for the backward."""
+    per-sample decoder weights, rays, and fixed upstream gradients for the backward.  Sample g of the global batch is
+    seeded by g alone, so the job renders the same 32 samples however many ranks share them."""
     from enarf_gan_b200 import hostmath, rendering, synthetic as S
-    seed = SEED + 1000 * rank
-    inp = S.make_inputs(B, SIZE, seed=seed)
-    tp = S.make_triplane(B, num_part=PARTS, seed=seed).to(device)
+    seed = SEED
+    per = [S.make_inputs(1, SIZE, seed=SEED + 17 * (first + i)) for i in range(B)]
+    inp = {k: torch.cat([q[k] for q in per], dim=0) for k in per[0]}
+    tp = torch.cat([S.make_triplane(1, num_part=PARTS, seed=SEED + 17 * (first + i)) for i in range(B)]).to(device)
     frames, bl = hostmath.part_frames(inp["pose_to_camera"], inp["bone_length"], "center+head", S.SMPL_PARENTS)
     pose = hostmath.scaled_pose(frames, 3.0).to(device)
     cframes, clen = hostmath.canonical_part_frames(S.canonical_pose(), S.SMPL_PARENTS, "center+head")
     cscale = (clen[None, :, None] / bl / 3.0)[:, :, 0].to(device)
-    g = torch.Generator().manual_seed(seed)
+    g = torch.Generator().manual_seed(seed + first)
     z = torch.randn(B, 256, generator=g)
     decoder = []
     for cin, cout in ((32, 64), (64, 64), (64, 4)):
@@ -142,12 +159,11 @@ def step_device(w, step_idx, timer=None, world=None):
     dev = w["pose"].device
     scene = timed("repack", lambda: ops.SceneBuffers(w["pose"], w["cscale"], w["canon"], w["tri_plane"], w["decoder"]))
     pose_all = w["pose"]
-    if world is not None:          # batch-global near/far (rendering.py:15-17) across the sharded batch
-        import torch.distributed as dist
-        gathered = [torch.empty_like(w["pose"]) for _ in range(world)]
-        dist.all_gather(gathered, w["pose"])
-        pose_all = torch.cat(gathered, dim=0)
-    nearfar = ops.near_far(pose_all)
+    if world is not None:          # batch-global near/far (rendering.py:15-17) across the sharded batch: the
+        from enarf_gan_b200 import rendering   # path's only exchange, two all_reduces of one float (MIN, MAX)
+        nearfar = timed("near_far_allreduce", lambda: rendering.global_near_far(w["pose"]))
+    else:
+        nearfar = ops.near_far(pose_all)
     dmin, dmax, direction, valid = timed("depth_range", lambda: ops.depth_range(w["img"], w["inv_K"], w["pose"], nearfar))
     wb = timed("coarse", lambda: ops.render_coarse(scene, dmin, dmax, direction, NC))
     bins = timed("fine_sample", lambda: ops.fine_sample(wb, NF, seed=step_idx))
@@ -170,6 +186,7 @@ def step_device(w, step_idx, timer=None, world=None):
     timed("fine_bwd", bwd)
     timed("unpack", lambda: ops.unpack_plane_grads(d_feat, d_tp, accumulate=False))
     w["last"] = (color, mask, d_tp, dw, bins, dmin, dmax, direction)
+    w["ckpt_tile_base"] = pairs.tile_base
     return 8   # repack, near_far, depth_range, coarse, fine_sample, fine_fwd, fine_bwd, unpack
 
 
@@ -238,71 +255,199 @@ def step_e2e(gen, host, out_img, out_loss, device):
 
 
 # ----------------------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference path, timed on the host cores (bounded sample)
+# Reference arms.  The UNMODIFIED reference (its eager grid_sample path) is imported through the test harness
+# (tests/golden/ref_harness.py: /root/reference here, the staged archive oracle/_ref/reference_py.zip on the GPU box)
+# and timed on the host cores (``cpu_baseline``, ``--impl reference``) and on this GPU (``gpu_reference``).  Only if
+# the archive is missing does the CPU arm fall back to the oracle port.  None of this is on the product path.
 # ----------------------------------------------------------------------------------------------------
-CPU_SAMPLE = "B=1, 128x128 rays (one sample of the config-2 batch), 48+48 samples/ray, P=24, fp32, forward+backward through oracle/enarf_oracle.py"
-
-
-def cpu_step(state=None):
-    """One fwd+bwd render of the bounded sample with the CPU oracle.  Returns (state, rays, seconds)."""
-    for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests")):
+def _paths():
+    for p in (os.path.join(ROOT, "oracle"), os.path.join(ROOT, "tests"), os.path.join(ROOT, "tests", "golden")):
         if p not in sys.path:
             sys.path.insert(0, p)
+
+
+def reference_available():
+    _paths()
+    import ref_harness as H
+    return H.available()
+
+
+class ReferenceRun:
+    """The reference's TriNARFGenerator on a synthetic batch of ``B`` samples at ``size`` x ``size`` rays."""
+
+    def __init__(self, B, size, device, seed=1235, train=True):
+        _paths()
+        import ref_harness as H
+        from enarf_gan_b200 import synthetic as S
+        H.set_device(device)
+        self.dev = torch.device(device)
+        self.B, self.size = B, size
+        gen = H.build_generator(size, S.canonical_pose(), S.SMPL_PARENTS, seed=seed, Nc=NC, Nf=NF)
+        self.gen = gen.to(self.dev)
+        self.gen.train(train)
+        inp = S.make_inputs(B, size, seed=seed)
+        self.inp = {k: v.to(self.dev) for k, v in inp.items()}
+        self.tp = S.make_triplane(B, num_part=PARTS, seed=seed).to(self.dev).requires_grad_(train)
+        self.z = S.make_latent(B, seed=seed).to(self.dev)
+        nerf = self.gen.nerf
+        orig = nerf._forward
+
+        def forward_with_planes(*a, **k):       # models/narf.py:187-193: per-sample planes through model_input
+            a = list(a)
+            a[8]["tri_plane_feature"] = self.tp
+            return orig(*a, **k)
+
+        nerf._forward = forward_with_planes
+
+    def step(self, backward=True):
+        i = self.inp
+        self.gen.zero_grad(set_to_none=True)
+        self.tp.grad = None
+        with torch.set_grad_enabled(backward):
+            color, mask, fw, fd = self.gen(i["pose_to_camera"], i["pose_to_world"], i["bone_length"], self.z,
+                                           i["inv_intrinsics"])
+            if backward:
+                loss = (color ** 2).mean() + ((1 - mask) ** 2).mean()
+                loss.backward()
+        return self.B * self.size * self.size
+
+
+def cpu_reference(max_seconds=25.0, min_steps=3):
+    """-> cpu_baseline dict: the reference's own CPU path, fwd+bwd, on ONE 128 x 128 sample of the workload
+    (B = 1: a bounded sample; per-ray normalisation makes it comparable), all host threads, median of the steps; plus
+    BASELINE.md section 2's figure: config 1 exactly (B=1, 64 x 64, forward only), 2 warm-up + 5 timed, median."""
+    torch.set_num_threads(os.cpu_count() or 1)
+    if not reference_available():
+        return cpu_port()
+    run = ReferenceRun(1, SIZE, "cpu", seed=1235)
+    rays = run.step()                           # warm-up (allocator, thread pool)
+    times = []
+    while len(times) < min_steps or (sum(times) < max_seconds * 0.6 and len(times) < 9):
+        t0 = time.perf_counter()
+        run.step()
+        times.append(time.perf_counter() - t0)
+    med = sorted(times)[len(times) // 2]
+    out = {"value": rays / med, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "reference",
+           "sample": f"B=1, {SIZE}x{SIZE} rays (one sample of the workload), {NC}+{NF} samples/ray, P={PARTS}, fp32, forward+"
+                     f"backward through the UNMODIFIED reference TriNARFGenerator (eager grid_sample path) on the host cores, "
+                     f"median of {len(times)} steps after 1 warm-up", "seconds": sum(times), "ms_per_step": med * 1e3}
+    c1 = ReferenceRun(1, 64, "cpu", seed=1235, train=False)
+    for _ in range(2):
+        c1.step(backward=False)
+    t1 = []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        r1 = c1.step(backward=False)
+        t1.append(time.perf_counter() - t0)
+    m1 = sorted(t1)[2]
+    out["config1_forward"] = {"value": r1 / m1, "unit": "rays/s", "points_per_s": r1 / m1 * (NC + NF), "ms": m1 * 1e3,
+                              "what": "BASELINE configs[0] exactly: B=1, 64x64 rays, 48+48 samples, forward render, "
+                                      "reference on CPU, 2 warm-up + 5 timed, median"}
+    return out
+
+
+def cpu_port():
+    """Fallback when the reference archive is absent: the oracle port (torch-CPU restatement), same bounded sample."""
+    _paths()
     import enarf_oracle as O
     from enarf_gan_b200 import synthetic as S
-    torch.set_num_threads(os.cpu_count() or 1)
-    if state is None:
-        B, size = 1, 128
-        inp = S.make_inputs(B, size, seed=1235)
-        tp = S.make_triplane(B, seed=1235)
-        g = torch.Generator().manual_seed(1235)
-        layers = [dict(mod_weight=torch.randn(cin, 256, generator=g), mod_bias=torch.ones(cin),
-                       weight=torch.randn(cout, cin, generator=g), bias=0.3 * torch.randn(cout, generator=g))
-                  for cin, cout in ((32, 64), (64, 64), (64, 4))]
-        sc = O.Scene(inp["pose_to_camera"], inp["bone_length"], inp["inv_intrinsics"], tp, layers,
-                     torch.randn(B, 256, generator=g), S.canonical_pose(), S.SMPL_PARENTS)
-        state = (sc, O.whole_image_grid(size, size, B), size)
-    sc, img, size = state
-    t0 = time.perf_counter()
-    sc.tri_plane = sc.tri_plane.detach().requires_grad_()
-    sc.eff = [(w.detach().requires_grad_(), b.detach().requires_grad_()) for w, b in sc.eff]
-    out = O.render(sc, img, NC, NF, {"mode": "torch"})
-    loss = (out["color"] ** 2).mean() + ((1 - out["mask"]) ** 2).mean()
-    loss.backward()
-    return state, size * size, time.perf_counter() - t0
+    B, size = 1, SIZE
+    inp = S.make_inputs(B, size, seed=1235)
+    tp = S.make_triplane(B, seed=1235)
+    g = torch.Generator().manual_seed(1235)
+    layers = [dict(mod_weight=torch.randn(cin, 256, generator=g), mod_bias=torch.ones(cin),
+                   weight=torch.randn(cout, cin, generator=g), bias=0.3 * torch.randn(cout, generator=g))
+              for cin, cout in ((32, 64), (64, 64), (64, 4))]
+    sc = O.Scene(inp["pose_to_camera"], inp["bone_length"], inp["inv_intrinsics"], tp, layers,
+                 torch.randn(B, 256, generator=g), S.canonical_pose(), S.SMPL_PARENTS)
+    img = O.whole_image_grid(size, size, B)
+    times = []
+    for i in range(4):
+        t0 = time.perf_counter()
+        sc.tri_plane = sc.tri_plane.detach().requires_grad_()
+        sc.eff = [(w.detach().requires_grad_(), b.detach().requires_grad_()) for w, b in sc.eff]
+        out = O.render(sc, img, NC, NF, {"mode": "torch"})
+        ((out["color"] ** 2).mean() + ((1 - out["mask"]) ** 2).mean()).backward()
+        if i:
+            times.append(time.perf_counter() - t0)
+    med = sorted(times)[len(times) // 2]
+    return {"value": size * size / med, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"B=1, {SIZE}x{SIZE} rays, {NC}+{NF} samples/ray, fwd+bwd through oracle/enarf_oracle.py (reference "
+                      "archive oracle/_ref/reference_py.zip not staged)", "seconds": sum(times), "ms_per_step": med * 1e3}
+
+
+def gpu_reference(device, B=2, steps=5, warmup=2):
+    """the reference's eager PyTorch path on THIS B200, fwd+bwd, CUDA-event timed."""
+    if not reference_available():
+        return {"unavailable": "oracle/_ref/reference_py.zip not staged"}
+    try:
+        run = ReferenceRun(B, SIZE, str(device), seed=1235)
+        for _ in range(warmup):
+            run.step()
+        torch.cuda.synchronize()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        for a, b in ev:
+            a.record()
+            rays = run.step()
+            b.record()
+        torch.cuda.synchronize()
+        ms = sorted(a.elapsed_time(b) for a, b in ev)[steps // 2]
+        peak = torch.cuda.max_memory_allocated() / 2 ** 30
+        del run
+        torch.cuda.empty_cache()
+        return {"value": rays / (ms * 1e-3), "unit": "rays/s", "ms_per_step": ms, "batch": B, "peak_mem_gib": peak,
+                "what": f"UNMODIFIED reference TriNARFGenerator.forward + backward (eager grid_sample path) on this GPU, "
+                        f"B={B} x {SIZE}x{SIZE} rays, {NC}+{NF} samples, median of {steps} after {warmup} warm-up"}
+    except Exception as e:  # noqa: BLE001  (a baseline must never take the bench line down)
+        torch.cuda.empty_cache()
+        return {"unavailable": f"{type(e).__name__}: {e}"[:300]}
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the CPU port of the reference path on all host threads, same metric / config."""
+    """--impl reference: the reference's own CPU implementation of the path on all host threads, same metric /
+    config; every step is the bounded sample (one 128 x 128 sample of the batch)."""
     if rank != 0:
         return
-    state = None
-    for _ in range(max(1, min(args.warmup, 1))):
-        state, rays, _ = cpu_step(state)
-    times = []
-    for _ in range(max(1, min(args.steps, 5))):
-        state, rays, dt = cpu_step(state)
-        times.append(dt)
-    dt = sum(times) / len(times)
-    value = rays / dt
-    line = base_line(args, value, dt * 1e3, len(times))
+    torch.set_num_threads(os.cpu_count() or 1)
+    if reference_available():
+        run = ReferenceRun(1, SIZE, "cpu", seed=1235)
+        kind, what = "reference", "UNMODIFIED reference TriNARFGenerator (eager grid_sample path) forward+backward on the host cores"
+        step = run.step
+    else:
+        kind, what = "port", "oracle/enarf_oracle.py (reference archive not staged)"
+        step = None
+    if step is None:
+        cb = cpu_port()
+        value, ms, steps = cb["value"], cb["ms_per_step"], 3
+    else:
+        for _ in range(max(1, min(args.warmup, 2))):
+            rays = step()
+        times = []
+        for _ in range(max(1, min(args.steps, 8))):
+            t0 = time.perf_counter()
+            rays = step()
+            times.append(time.perf_counter() - t0)
+        dt = sum(times) / len(times)
+        value, ms, steps = rays / dt, dt * 1e3, len(times)
+    line = base_line(args, value, ms, steps, world)
+    sample = f"each step = one {SIZE}x{SIZE}-ray sample (B=1) of the workload, {NC}+{NF} samples/ray, fwd+bwd; {what}"
     line.update(impl="reference", gpu_launches=0,
-                cpu_baseline={"value": value, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
-                              "sample": CPU_SAMPLE},
+                cpu_baseline={"value": value, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": kind, "sample": sample},
                 e2e={"value": value, "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0})
-    line["config"]["note"] = ("/root/reference cannot travel to the GPU box; the arm times oracle/enarf_oracle.py, the "
-                              "torch-CPU restatement pinned against the reference's own outputs")
     print(json.dumps(line))
 
 
-def base_line(args, value, ms, steps):
-    return {"metric": "rendered_rays_per_s_fwd_bwd", "value": value, "unit": "rays/s", "n_gpus": args.gpus,
-            "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"ENARF-GAN generator render fwd+bwd, {SIZE}x{SIZE} rays/sample, {NC}+{NF} samples/ray, "
-                                   f"P={PARTS} parts, batch {args.batch} per GPU (BASELINE configs[1]/[2] shapes)",
-                       "global_batch": args.batch * max(1, args.gpus), "rays_per_step": args.batch * max(1, args.gpus) * SIZE * SIZE,
-                       "points_per_ray": NC + NF, "parallelism": f"sample-sharded x{max(1, args.gpus)}, no data-path collective",
+def base_line(args, value, ms, steps, world):
+    weak = args.batch is not None
+    gb = args.batch * world if weak else args.global_batch
+    return {"metric": "rendered_rays_per_s_fwd_bwd", "value": value, "unit": "rays/s", "n_gpus": world,
+            "steps": steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak" if weak else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": (f"BASELINE configs[2]: ENARF-GAN generator render fwd+bwd (tri-plane + MLP gradients), "
+                                    f"{SIZE}x{SIZE} rays/sample, {NC}+{NF} samples/ray, P={PARTS} parts, global batch {gb} "
+                                    + (f"= {args.batch} per GPU (weak)" if weak else f"sample-sharded over {world} GPU(s)")),
+                       "global_batch": gb, "rays_per_step": gb * SIZE * SIZE,
+                       "points_per_ray": NC + NF, "parallelism": f"sample-sharded x{world}; only exchange: 2-float near/far all_reduce",
                        "l2": "inputs larger than L2 (tri-planes 44 MB/sample x batch, re-packed every step)"}}
 
 
@@ -321,7 +466,9 @@ def main():
         dist.init_process_group("nccl", device_id=device)
     from enarf_gan_b200 import _abi
     _abi.lib()
-    w = build_workload(rank, args.batch, device)
+    first, B = local_batch(args, rank, world)
+    assert B > 0, "more ranks than samples: use render_entire_img_sharded (ray blocks) for B < G"
+    w = build_workload(first, B, device)
     wd = world if world > 1 else None
 
     def sync():
@@ -346,6 +493,7 @@ def main():
     sync()
     ms = t0.elapsed_time(t1) / args.steps
     kt = timer.totals()
+    overflow = int((w["ckpt_tile_base"] < 0).sum().item())     # tiles of the last step whose pairs did not fit the checkpoint
     # ---- end-to-end arm (host buffers in, image + loss out) ----
     gen, host, out_img, out_loss, h2d, d2h = build_e2e(w, device)
     for _ in range(max(3, args.warmup)):
@@ -359,54 +507,70 @@ def main():
     sync()
     ms_e2e = e0.elapsed_time(e1) / args.steps
     clk = clocks.stop() if rank == 0 else None
+    per_rank = None
     if world > 1:
-        t = torch.tensor([ms, ms_e2e], device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, ms_e2e = t.tolist()
+        mine = torch.tensor([ms, ms_e2e, kt.get("near_far_allreduce", 0.0)], device=device)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = [[round(v, 4) for v in t.tolist()] for t in allr]
+        ms, ms_e2e = max(r[0] for r in per_rank), max(r[1] for r in per_rank)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    rays = args.batch * world * SIZE * SIZE
+    gb = args.batch * world if args.batch is not None else args.global_batch
+    rays = gb * SIZE * SIZE
     value = rays / (ms * 1e-3)
-    line = base_line(args, value, ms, args.steps)
-    line["n_gpus"] = world
+    line = base_line(args, value, ms, args.steps, world)
     line["clocks"] = clk
     line["gpu_launches"] = launches
     line["points_per_s"] = value * (NC + NF)
     line["e2e"] = {"value": rays / (ms_e2e * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                    "ms_per_step": ms_e2e, "api": "TriNARFGenerator.forward + loss.backward (pinned host inputs)"}
+    if per_rank is not None:
+        # [device ms, e2e ms, near/far all_reduce ms] of every rank: the spread is the load imbalance (each rank's samples
+        # have their own mean valid parts per point), the third column the only collective on the path
+        line["per_rank_ms"] = per_rank
+    line["samples_per_gpu"] = B
+    line["pair_checkpoint_overflow_tiles"] = overflow
     # ---- roofline of the dominant kernel (rank 0's launches) ----
     (vc, ac), (vf, af) = mean_valid_parts(w)
-    R = args.batch * SIZE * SIZE
+    R = B * SIZE * SIZE
+    # per (point, valid part) 396*s bytes, per ray the streamed I/O
     alg = {"coarse": R * NC * vc * 396 * 4 + R * (20 + NC * 4),
            "fine_fwd": R * NF * vf * 396 * 4 + R * (20 + NF * 4 + (NF - 1) * 4 + NF * 4 + NF * 16),
            "fine_bwd": 2 * R * NF * vf * 396 * 4 + R * (20 + NF * 4 + NF * 16)}
     dom = max(alg, key=lambda k: kt[k])
     peak, peak_src = peaks()
     achieved = alg[dom] / (kt[dom] * 1e-3) / 1e9
-    traffic = traffic_src = None     # measured DRAM bytes per launch of that kernel, from the committed ncu capture
-    tpath = os.path.join(ROOT, "profiles", "ncu_traffic_r1.json")
-    if os.path.exists(tpath) and args.batch == 8:
+    roof = {"bound": "l2-atomics + issue (NOT hbm: the planes are L2-resident, see dram_frac)", "kernel": dom,
+            "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
+            "frac_definition": "SURVEY 8(d) algorithmic gather bytes / kernel time / measured HBM copy peak; these bytes are "
+                               "served by L2, so frac is an L2-gather rate expressed in HBM units, not DRAM utilisation",
+            "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kt[dom],
+            "mean_valid_parts_per_point": {"coarse": vc, "fine": vf}, "active_point_fraction": {"coarse": ac, "fine": af},
+            "kernel_ms_all": kt, "kernel_share_of_step": kt[dom] / ms, "traffic": None}
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic_r2.json")   # measured DRAM bytes per launch (ncu --set full)
+    if os.path.exists(tpath):
         tj = json.load(open(tpath))
-        if dom in tj["kernels"]:
-            traffic = tj["kernels"][dom]["dram_bytes_read"] + tj["kernels"][dom]["dram_bytes_write"]
-            traffic_src = tj["source"]
-    line["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                        "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                        "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kt[dom],
-                        "mean_valid_parts_per_point": {"coarse": vc, "fine": vf},
-                        "active_point_fraction": {"coarse": ac, "fine": af},
-                        "kernel_ms_all": kt, "kernel_share_of_step": kt[dom] / ms}
-    if not args.no_cpu_baseline:
-        state, crays, _ = cpu_step(None)   # warm-up (allocator, thread pool)
-        cts = []
-        while len(cts) < 3 and sum(cts) < 20.0:   # about 10 s of CPU work on the box's 16 threads
-            state, crays, dt = cpu_step(state)
-            cts.append(dt)
-        dt = sum(cts) / len(cts)
-        line["cpu_baseline"] = {"value": crays / dt, "unit": "rays/s", "cores": torch.get_num_threads(), "kind": "port",
-                                "sample": CPU_SAMPLE + f", mean of {len(cts)} steps", "seconds": sum(cts)}
+        if dom in tj["kernels"] and tj.get("samples_per_gpu") == B:
+            k = tj["kernels"][dom]
+            roof["traffic"] = k["dram_bytes_read"] + k["dram_bytes_write"]
+            roof["traffic_source"] = tj["source"]
+            roof["dram_frac"] = roof["traffic"] / (kt[dom] * 1e-3) / 1e9 / peak
+    if dom == "fine_bwd":
+        # the floor the backward cannot go under: its reductions at the measured L2-resident rates
+        # (scripts/microbench/red_rate.cu, profiles/red_rate_r1.txt): 12 x 8 lane-level red.v4 per pair at 381.5 G/s and
+        # 12 scattered 4-byte reductions per pair at 195.6 G/s
+        pairs = R * NF * vf
+        floor_ms = (pairs * 96 / 381.5e9 + pairs * 12 / 195.6e9) * 1e3
+        roof["l2_red_floor_ms"] = floor_ms
+        roof["l2_red_frac"] = floor_ms / kt[dom]
+    line["roofline"] = roof
+    if not args.no_gpu_reference and world == 1:
+        line["gpu_reference"] = gpu_reference(device)
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_reference()
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -96,8 +96,29 @@ def ptr(t, dtype=torch.float32, allow_none=False):
         raise TypeError(f"expected {dtype}, got {t.dtype}")
     if not t.is_contiguous():
         raise ValueError("tensor must be contiguous")
+    if t.device.index != torch.cuda.current_device():
+        # the library launches on the current device's stream: refuse rather than launch on the wrong GPU
+        raise RuntimeError(f"tensor on {t.device} but the current device is cuda:{torch.cuda.current_device()}: call "
+                           "under `with torch.cuda.device(tensor.device)` (rendering.render / render_rays do)")
     return t.data_ptr()
 
 
 def stream_ptr(device=None):
     return torch.cuda.current_stream(device).cuda_stream
+
+
+def on_device_of(index_or_name):
+    """Decorator: run the wrapped function with the CUDA device of one of its tensor arguments current, so that a
+    caller who never called torch.cuda.set_device still launches on the GPU that owns the tensors."""
+    import functools
+
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapper(*args, **kwargs):
+            t = kwargs.get(index_or_name) if isinstance(index_or_name, str) else args[index_or_name]
+            if isinstance(t, torch.Tensor) and t.is_cuda and t.device.index != torch.cuda.current_device():
+                with torch.cuda.device(t.device):
+                    return fn(*args, **kwargs)
+            return fn(*args, **kwargs)
+        return wrapper
+    return deco

@@ -16,15 +16,23 @@ void enarf_set_error(const char* fmt, ...) {
 extern "C" const char* enarf_last_error(void) { return g_err; }
 extern "C" int enarf_version(void) { return 140; }
 
+// SM count of the CURRENT device (the one the caller's pointers live on), cached per device id: a process that
+// drives several GPUs gets each one's own grid size.  Benign race: concurrent first calls store the same value.
 int enarf_sm_count() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        if (sms <= 0) sms = 148;
+    static int sms[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        return v > 0 ? v : 148;
     }
-    return sms;
+    if (!sms[dev]) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        sms[dev] = v > 0 ? v : 148;
+    }
+    return sms[dev];
 }
 
 int enarf_check_scene(const enarf_scene_t* sc, const char* who) {
@@ -45,8 +53,10 @@ int enarf_check_scene(const enarf_scene_t* sc, const char* who) {
 }
 
 // Dynamic tile scheduling needs one zeroed int per launch.  The library must not allocate, so the counters are
-// slots of a static device array handed out round-robin: launches stay independent unless more than
-// ENARF_COUNTER_SLOTS of them are in flight at once.
+// slots of a static device array (one copy per device: cudaGetSymbolAddress resolves it for the current device)
+// handed out round-robin by a process-wide atomic cursor: launches stay independent unless more than
+// ENARF_COUNTER_SLOTS of them are in flight at once.  This cursor and the SM-count cache above are the library's
+// only mutable globals besides the thread-local error string.
 #define ENARF_COUNTER_SLOTS 4096
 __device__ int g_tile_counters[ENARF_COUNTER_SLOTS];
 static unsigned g_next_slot = 0;

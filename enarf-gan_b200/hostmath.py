@@ -67,6 +67,19 @@ def modulated_weight(weight, mod_weight, mod_bias, style):
     return torch.nn.functional.normalize(w, dim=-1)
 
 
+def bone_length_encoding(bone_length, num_frequency, num_bone):
+    """The conditioning vector the reference hands to its StyleGAN2-ADA tri-plane / flow generator:
+    ``multi_part_positional_encoding(bone_length, L, num_bone)[:, :, 0]`` (libraries/NeRF/utils.py:46-71, called at
+    models/narf.py:286-289).  bone_length (B,num_bone,1) -> (B, num_bone*2L): per part
+    [sin(l 2^0 pi) .. sin(l 2^(L-1) pi), cos(l 2^0 pi) .. cos(l 2^(L-1) pi)], zeroed for parts with |l| > 1."""
+    B = bone_length.shape[0]
+    l = bone_length.reshape(B, num_bone, 1)
+    ang = l * 2 ** torch.arange(num_frequency, device=l.device) * math.pi           # (B,P,L): (l * 2^i) * pi
+    enc = torch.cat([torch.sin(ang), torch.cos(ang)], dim=2)
+    enc = enc * (1 - (l.abs() > 1).to(enc.dtype))
+    return enc.reshape(B, num_bone * 2 * num_frequency)
+
+
 def random_scene(inp, tri_plane, seed=0, device="cuda", origin_location="center+head", coordinate_scale=3.0,
                  plane_dtype=torch.float32):
     """A SceneBuffers with random-init decoder weights for synthetic benchmarks / smoke runs."""

@@ -16,6 +16,7 @@ import torch
 from torch import nn
 
 from . import hostmath, ops, rendering
+from ._abi import on_device_of
 
 _UNSUPPORTED = ("selector_mlp", "no_selector", "clamp_mask", "multiply_density_with_triplane_wieght",
                 "constant_trimask")
@@ -105,6 +106,7 @@ class TriPlaneNARF(nn.Module):
         self.w_dim, self.feat_dim = 512, 32
         self.view_dependent = False
         self.num_bone = num_bone - 1 if self.origin_location in ("center", "center_fixed") else num_bone
+        self.num_frequency_for_other = _cfg(config, "num_frequency_for_other", 4)    # NeRF/base.py:29
         self.parent_id = np.asarray(parent)
         self.plane_dtype = plane_dtype
         self.rng_mode = "torch"      # "torch": the reference's multinomial/uniform_ stream; "philox": in-kernel
@@ -117,7 +119,8 @@ class TriPlaneNARF(nn.Module):
         elif _cfg(config, "deformation_field", False):
             # DSO "denarf" (narf.py:39-58): one canonical tri-plane, warped per sample by a 6-channel flow field.
             # The flow head itself is the StyleGAN2-ADA generator (out of scope): pass it as ``flow_generator``
-            # (called as flow_generator(z, bone_length, truncation_psi=...) -> (B,6,256,256)) or hand the flow
+            # (called like the reference's: flow_generator(z, c, truncation_psi=...) -> (B,6,256,256) with c the
+            # positional encoding of the bone lengths, ``encoded_bone_length``) or hand the flow
             # over as model_input["flow"].
             self.deformation_field = True
             self.tri_plane = nn.Parameter(torch.zeros(1, 32 * 3 + self.num_bone * 3, 256, 256))
@@ -141,10 +144,14 @@ class TriPlaneNARF(nn.Module):
         return hostmath.part_frames(pose_to_camera, bone_length, self.origin_location, self.parent_id)
 
     # ---- tri-plane ------------------------------------------------------------------------------------
+    def encoded_bone_length(self, bone_length):
+        """c of the StyleGAN2-ADA generators (c_dim = 2 L num_bone, narf.py:79-82,286-289)."""
+        return hostmath.bone_length_encoding(bone_length, self.num_frequency_for_other, self.num_bone)
+
     def compute_flow(self, z, bone_length, truncation_psi=1):
         if not hasattr(self, "flow_generator"):
             raise RuntimeError("deformation_field needs a flow_generator module or model_input['flow']")
-        return self.flow_generator(z, bone_length, truncation_psi=truncation_psi)
+        return self.flow_generator(z, self.encoded_bone_length(bone_length), truncation_psi=truncation_psi)
 
     def warped_planes(self, flow):
         """flow (B,6,H,W) -> (feature planes (B,3,H,W,32) channels-last in ``plane_dtype``, probability planes
@@ -167,7 +174,7 @@ class TriPlaneNARF(nn.Module):
         if not hasattr(self, "tri_plane_gen"):
             raise RuntimeError("no tri-plane source: pass constant_triplane=True, a tri_plane_gen module or "
                                "model_input['tri_plane_feature']")
-        return self.tri_plane_gen(z, bone_length, truncation_psi=truncation_psi)
+        return self.tri_plane_gen(z, self.encoded_bone_length(bone_length), truncation_psi=truncation_psi)
 
     def build_scene(self, pose_scaled, model_input: Dict):
         """SceneBuffers for one render call + the autograd-tracked tensors behind it."""
@@ -195,6 +202,7 @@ class TriPlaneNARF(nn.Module):
         return scene, tri_plane, decoder
 
     # ---- point query (models/narf.py:176-211) ---------------------------------------------------------
+    @on_device_of(1)
     def calc_density_and_color_from_camera_coord_v2(self, position, pose_to_camera, ray_direction, model_input):
         """position (B,3,n) in the scaled camera frame -> density (B,1,n), color (B,3,n).  Forward only."""
         scene, _, _ = self.build_scene(pose_to_camera, model_input)
@@ -202,6 +210,7 @@ class TriPlaneNARF(nn.Module):
             den, col, _ = ops.density_query(scene, position.to(torch.float32).contiguous())
         return den, col
 
+    @on_device_of(1)
     def density_grid(self, pose_to_camera, center, voxel_size=0.003, model_input=None, chunk=1 << 24):
         """The density volume ``create_mesh`` feeds to marching cubes (libraries/NARF/mesh_rendering.py:50-71):
         (2/voxel_size + 1)^3 points on a regular grid around ``center`` (1,3,1), in the scaled camera frame, queried

@@ -325,19 +325,26 @@ class RenderFine(torch.autograd.Function):
         scene = ctx.scene
         B, dev = scene.B, ctx.saved_tensors[0].device
         need_tp = ctx.needs_input_grad[5]
-        # the feature channels of d_tp are overwritten by unpack_plane_grads: only the probability channels
-        # (scattered into directly) and the channels-last scratch need zero-filling
-        d_tp = torch.empty(ctx.tp_shape, device=dev) if need_tp else torch.zeros(ctx.tp_shape, device=dev)
         d_feat = torch.zeros(B, 3, scene.H, scene.W, FEAT_DIM, device=dev)
         if need_tp:
-            # per sample: each slice is contiguous, so the fill is the vectorised one (the strided view of the whole
-            # batch falls back to torch's generic element-wise fill: 78 us instead of ~25 us for 151 MB)
+            # the feature channels of d_tp are overwritten by unpack_plane_grads: only the probability channels
+            # (scattered into directly) and the channels-last scratch need zero-filling.  Per sample: each slice is
+            # contiguous, so the fill is the vectorised one (the strided view of the whole batch falls back to torch's
+            # generic element-wise fill: 78 us instead of ~25 us for 151 MB)
+            d_tp = torch.empty(ctx.tp_shape, device=dev)
             for b in range(d_tp.shape[0]):
                 d_tp[b, FEAT_DIM * 3:].zero_()
-        dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_tp[:, FEAT_DIM * 3:], d_tp.stride(0))
+            d_prob, stride = d_tp[:, FEAT_DIM * 3:], d_tp.stride(0)
+        else:
+            # only the decoder wants gradients: the kernel still needs somewhere to scatter d(probability), but not
+            # a full NCHW tri-plane gradient
+            d_tp = None
+            d_prob = torch.zeros(B, ctx.tp_shape[1] - FEAT_DIM * 3, scene.H, scene.W, device=dev)
+            stride = d_prob.stride(0)
+        dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_prob, stride)
         if need_tp:
             unpack_plane_grads(d_feat, d_tp, accumulate=False)
-        return (None, None, None, None, None, d_tp if need_tp else None) + dec
+        return (None, None, None, None, None, d_tp) + dec
 
 
 class RenderFinePlanes(torch.autograd.Function):

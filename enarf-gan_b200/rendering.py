@@ -10,6 +10,7 @@ from typing import Dict, Optional
 import torch
 
 from . import ops
+from ._abi import on_device_of
 
 NEAR_PLANE = 0.3   # rendering.py:249
 FAR_PLANE = 5.0    # rendering.py:138
@@ -24,6 +25,7 @@ def pixel_grid(render_size, patch_size, batchsize, device):
     return torch.stack([x, y, torch.ones_like(x)], dim=0)[None].expand(batchsize, 3, -1).contiguous()
 
 
+@on_device_of(1)
 def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rng="philox", seed=0,
                 idx=None, jitter=None, compact_b1=True, tri_plane=None, decoder=None, nearfar=None,
                 generator=None, return_intermediate=False, want_points=False):
@@ -88,6 +90,7 @@ def _scaled(model, pose_to_camera):
     return pose_to_camera
 
 
+@on_device_of(2)
 def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: float = 1, Nc: int = 64,
            Nf: int = 128, semantic_map: bool = False, return_intermediate: bool = False,
            camera_pose: Optional[torch.Tensor] = None, model_input: Dict = {}, _scene=None):
@@ -140,6 +143,7 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
     return out["color"], out["mask"], out["disparity"]
 
 
+@on_device_of(1)
 def render_entire_img(model, pose_to_camera, inv_intrinsics, camera_pose: Optional[torch.Tensor] = None,
                       render_size: int = 128, Nc: int = 64, Nf: int = 128, semantic_map: bool = False,
                       use_normalized_intrinsics: bool = False, no_grad: bool = True, model_input: Dict = {},
@@ -198,19 +202,18 @@ def global_near_far(pose_local, near0: float = NEAR_PLANE, far0: float = FAR_PLA
     """near/far over the WHOLE batch from this rank's shard of the (scaled) part frames (B_local,P,4,4).
 
     near = max(min t_z - sqrt3, near0), far = max(max t_z + sqrt3, far0) (rendering.py:15-17); the min / max
-    over ranks is one all_reduce each on a single float (NCCL on GPUs, gloo in the CPU tests).  Returns the
+    over ranks is ONE all_reduce(MAX) of the pair (-min, max) (NCCL on GPUs, gloo in the CPU tests).  Returns the
     2-element tensor ``ops.depth_range(..., nearfar=)`` expects; with no process group it is the local value.
     """
     import torch.distributed as dist
     tz = pose_local[:, :, 2, 3].to(torch.float32)
-    lo, hi = tz.min().reshape(1), tz.max().reshape(1)
+    ext = torch.stack([-tz.min(), tz.max()])           # one MAX reduction carries both extremes
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=group)
     sqrt3 = 3 ** 0.5
-    near = torch.clamp_min(lo - sqrt3, near0)
-    far = torch.clamp_min(hi + sqrt3, far0)
-    return torch.cat([near, far])
+    near = torch.clamp_min(-ext[0] - sqrt3, near0)
+    far = torch.clamp_min(ext[1] + sqrt3, far0)
+    return torch.stack([near, far])
 
 
 def shard_rays(n_rays: int, rank: int, world: int):

@@ -9,7 +9,10 @@
  *   - every pointer is a DEVICE pointer unless its comment says "host"; the caller owns every buffer
  *     (outputs, zero-initialised gradient buffers, scratch); the library never allocates or retains them;
  *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream); calls are asynchronous and
- *     never synchronise the device; the current device must be the one owning the pointers;
+ *     never synchronise the device; the current device must be the one owning the pointers (the Python binding
+ *     wraps every call in torch.cuda.device(tensor.device)); re-entrant: the only mutable process-wide state is a
+ *     per-device SM-count cache and the round-robin cursor of the per-device tile-counter slots (both benign under
+ *     concurrent callers), plus the thread-local error string;
  *   - every function returns 0 on success or an ENARF_ERR_* code; enarf_last_error() gives the message of
  *     the last failure on the calling thread; no exceptions cross the boundary;
  *   - all floating-point buffers are fp32 unless stated; tensors are dense row-major with the shape given.

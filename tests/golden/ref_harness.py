@@ -1,20 +1,27 @@
-"""Load the UNMODIFIED reference (/root/reference) on CPU so it can pin the oracle.
+"""Load the UNMODIFIED reference so it can pin the oracle and stand beside the kernels as the second oracle / baseline.
 
-Only usable in the authoring container (the GPU box has no /root/reference); it is imported solely by
-``tests/golden/make_golden.py`` and by the CPU tests that are skipped when the reference is absent.
-Reference files are never copied: they are read where they lie, a handful of hard-coded ``"cuda"``
-device strings are substituted in memory at import time, and five missing
-third-party modules are stubbed.
+The reference is imported from ``/root/reference`` where that exists (the authoring container) and otherwise from
+``oracle/_ref/reference_py.zip``, the byte-identical archive of its hot-path Python that ``oracle/build_ref.py`` packs
+(git-ignored build output; it travels to the GPU box).  Nothing is copied or edited on disk: a handful of hard-coded
+``"cuda"`` device strings are substituted in memory at import time so the same code runs on
+``DEVICE`` (CPU here, CUDA on the box), and the missing third-party modules are stubbed.  TEST / BASELINE
+INFRASTRUCTURE: imported only by ``tests/`` and ``bench.py``'s reference arm.
 """
 import importlib.abc
 import importlib.util
 import os
 import sys
 import types
+import zipfile
 
 import torch
 
-REF_ROOT = "/root/reference"
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ZIP = os.path.join(os.path.dirname(os.path.dirname(_HERE)), "oracle", "_ref", "reference_py.zip")
+# ENARF_REF_FROM_ARCHIVE=1 forces the archive even where the live tree exists (to test what the GPU box will see)
+REF_ROOT = "/root/reference" if (os.path.isdir("/root/reference/libraries")
+                                 and not os.environ.get("ENARF_REF_FROM_ARCHIVE")) else _ZIP
+DEVICE = torch.device("cpu")     # where the reference's hard-coded "cuda" tensors go; set_device() changes it
 
 _SUBST = {
     "libraries/NeRF/rendering.py": [
@@ -23,34 +30,58 @@ _SUBST = {
          "torch.empty(batchsize, 1, n, Nf, device=_DEV()).uniform_()"),
     ],
     "libraries/NeRF/ray_sampler.py": [('device="cuda"', 'device=_DEV()')],
-    "models/generator.py": [(".cuda(homo_img.device)", ".to(homo_img.device)")],
+    # the scatter buffer takes the dtype of its operands (float32 in the default run: no change) so that the
+    # fp64-cast reference runs
+    "libraries/triplane/sampling.py": [("dtype=torch.float32)", "dtype=position.dtype)")],
+    # device AND dtype of the pixel grid: identical to ``.float().cuda(...)`` in the default fp32 run, and lets the
+    # fp64-cast reference (ref_runner.run(dtype=float64)) keep its intrinsics in double
+    "models/generator.py": [("inv_intrinsics.float().cuda(homo_img.device)", "inv_intrinsics.to(homo_img)")],
 }
-_PRELUDE = "import torch as _t; _DEV = lambda: _t.device('cpu'); "
+_PRELUDE = "import sys as _s; _DEV = lambda: _s.modules['ref_harness'].DEVICE; "
+
+
+def set_device(device):
+    global DEVICE
+    DEVICE = torch.device(device)
+
+
+def _read(rel):
+    if os.path.isdir(REF_ROOT):
+        with open(os.path.join(REF_ROOT, rel)) as f:
+            return f.read()
+    with zipfile.ZipFile(REF_ROOT) as z:
+        return z.read(rel).decode()
+
+
+def _exists(rel):
+    if os.path.isdir(REF_ROOT):
+        return os.path.exists(os.path.join(REF_ROOT, rel))
+    with zipfile.ZipFile(REF_ROOT) as z:
+        return rel in z.namelist()
 
 
 class _Loader(importlib.abc.Loader):
-    def __init__(self, path, rel):
-        self.path, self.rel = path, rel
+    def __init__(self, rel):
+        self.rel = rel
 
     def create_module(self, spec):
         return None
 
     def exec_module(self, module):
-        with open(self.path) as f:
-            src = f.read()
+        src = _read(self.rel)
         for a, b in _SUBST[self.rel]:
             assert a in src, (self.rel, a)
             src = src.replace(a, b)
         src = _PRELUDE + src  # same line as the file's first statement: line numbers stay stable
-        module.__file__ = self.path
-        exec(compile(src, self.path, "exec"), module.__dict__)
+        module.__file__ = os.path.join(REF_ROOT, self.rel)
+        exec(compile(src, module.__file__, "exec"), module.__dict__)
 
 
 class _Finder(importlib.abc.MetaPathFinder):
     def find_spec(self, fullname, path, target=None):
         rel = fullname.replace(".", "/") + ".py"
-        if rel in _SUBST and os.path.exists(os.path.join(REF_ROOT, rel)):
-            return importlib.util.spec_from_loader(fullname, _Loader(os.path.join(REF_ROOT, rel), rel))
+        if rel in _SUBST and _exists(rel):
+            return importlib.util.spec_from_loader(fullname, _Loader(rel))
         return None
 
 
@@ -88,7 +119,7 @@ _installed = False
 
 
 def available() -> bool:
-    return os.path.isdir(os.path.join(REF_ROOT, "libraries"))
+    return os.path.isdir(os.path.join(REF_ROOT, "libraries")) or os.path.isfile(REF_ROOT)
 
 
 def install():
@@ -96,9 +127,13 @@ def install():
     global _installed
     if _installed:
         return
-    assert available(), "reference not present"
-    os.chdir(REF_ROOT)  # the reference appends relative paths to sys.path
+    assert available(), "reference not present (neither /root/reference nor oracle/_ref/reference_py.zip)"
+    sys.modules.setdefault("ref_harness", sys.modules[__name__])
+    # the reference appends "libraries/stylegan2_ada_pytorch" / "libraries/stylegan2_pytorch" relative to its own
+    # root to sys.path (triplane_nerf.py:13, custom_stylegan2/net.py:12): give the absolute equivalents instead of
+    # changing the working directory (both a directory tree and a zip archive work as import roots)
     sys.path.insert(0, REF_ROOT)
+    sys.path.append(os.path.join(REF_ROOT, "libraries", "stylegan2_ada_pytorch"))
     sys.meta_path.insert(0, _Finder())
 
     ident = type("Identity", (torch.nn.Module,), {"__init__": lambda self, *a, **k: torch.nn.Module.__init__(self),
@@ -112,7 +147,15 @@ def install():
     _stub("pytorch3d.renderer", **{n: None for n in names})
     _stub("pytorch3d.renderer.mesh", Textures=None)
     _stub("pytorch3d.structures", Meshes=None)
-    _stub("triplane_sampler_cuda")
+    ext = None
+    if torch.cuda.is_available():     # the reference's own extension, compiled unmodified by oracle/build_ref.py
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(_HERE)), "oracle"))
+        import build_ref
+        ext = build_ref.load()
+    if ext is not None:
+        sys.modules["triplane_sampler_cuda"] = ext
+    else:
+        _stub("triplane_sampler_cuda")
     _stub("easydict", EasyDict=_EasyDict)
     _stub("tqdm", tqdm=lambda x, *a, **k: x) if "tqdm" not in sys.modules else None
 
@@ -130,13 +173,27 @@ def install():
         def forward(self, x):
             return fused_leaky_relu(x, self.bias, self.negative_slope, self.scale)
 
-    def upfirdn2d(*a, **k):
-        raise NotImplementedError("upfirdn2d is off the hot path")
+    def upfirdn2d(x, kernel, up=1, down=1, pad=(0, 0)):
+        """Pure-torch stand-in for the StyleGAN2 op the discriminator's Blur layers call (the original JIT-compiles
+        CUDA at import): zero-stuff by ``up``, pad, correlate every channel with the flipped 2-D FIR, keep every
+        ``down``-th sample."""
+        B, C, H, W = x.shape
+        if up > 1:
+            z = x.new_zeros(B, C, H, up, W, up)
+            z[:, :, :, 0, :, 0] = x
+            x = z.reshape(B, C, H * up, W * up)
+        x = torch.nn.functional.pad(x, (pad[0], pad[1], pad[0], pad[1]))
+        k = torch.flip(kernel, (0, 1)).to(x)[None, None].expand(C, 1, -1, -1)
+        x = torch.nn.functional.conv2d(x, k, groups=C)
+        return x[:, :, ::down, ::down]
+
+    gradfix = types.SimpleNamespace(conv2d=torch.nn.functional.conv2d,
+                                    conv_transpose2d=torch.nn.functional.conv_transpose2d)
 
     _stub("libraries.stylegan2_pytorch.op", FusedLeakyReLU=FusedLeakyReLU, fused_leaky_relu=fused_leaky_relu,
-          upfirdn2d=upfirdn2d, conv2d_gradfix=None)
+          upfirdn2d=upfirdn2d, conv2d_gradfix=gradfix)
     _stub("op", FusedLeakyReLU=FusedLeakyReLU, fused_leaky_relu=fused_leaky_relu, upfirdn2d=upfirdn2d,
-          conv2d_gradfix=None)
+          conv2d_gradfix=gradfix)
     _installed = True
 
 
