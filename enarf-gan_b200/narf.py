@@ -256,9 +256,14 @@ class TriPlaneNARF(nn.Module):
         model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
         pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
         with torch.set_grad_enabled(not no_grad):
-            if self.deformation_field:      # same hoisting as NARF/base.py:59-60, in the hand-off layout
-                model_input["planes"] = self.warped_planes(self.compute_flow(z[:1], bone_length[:1], truncation_psi))
+            # NARF/base.py:59-60 hoists the plane generation out of the chunk loop.  It hands the generator the
+            # UNtransformed bone_length there, which only works where transform_pose leaves it alone ("center",
+            # "center_fixed"; with "center+head" its positional encoding cannot even be reshaped to 24 parts): the
+            # transformed lengths are the same numbers in those cases and also work for "center+head".
+            bl = model_input["bone_length"]
+            if self.deformation_field:      # in the hand-off layout
+                model_input["planes"] = self.warped_planes(self.compute_flow(z[:1], bl[:1], truncation_psi))
             else:
-                model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bone_length)   # NARF/base.py:59-60
+                model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bl)
         return rendering.render_entire_img(self, pose_to_camera, inv_intrinsics, camera_pose, render_size, Nc, Nf,
                                            semantic_map, use_normalized_intrinsics, no_grad, model_input, bbox=bbox)

@@ -27,7 +27,7 @@ _SUBST = {
     "libraries/NeRF/rendering.py": [
         ('device="cuda"', 'device=_DEV()'),
         ("torch.cuda.FloatTensor(batchsize, 1, n, Nf).uniform_()",
-         "torch.empty(batchsize, 1, n, Nf, device=_DEV()).uniform_()"),
+         "_s.modules['ref_harness'].draw_jitter(batchsize, 1, n, Nf)"),
     ],
     "libraries/NeRF/ray_sampler.py": [('device="cuda"', 'device=_DEV()')],
     # the scatter buffer takes the dtype of its operands (float32 in the default run: no change) so that the
@@ -38,6 +38,16 @@ _SUBST = {
     "models/generator.py": [("inv_intrinsics.float().cuda(homo_img.device)", "inv_intrinsics.to(homo_img)")],
 }
 _PRELUDE = "import sys as _s; _DEV = lambda: _s.modules['ref_harness'].DEVICE; "
+
+
+FORCED_JITTER = None   # tests can pin the fine pass's jitter (ref_runner.run(force_draws=...))
+
+
+def draw_jitter(*shape):
+    """rendering.py:194 (``torch.cuda.FloatTensor(batchsize, 1, n, Nf).uniform_()``) on DEVICE, or the pinned draw."""
+    if FORCED_JITTER is not None:
+        return FORCED_JITTER.reshape(shape).to(DEVICE)
+    return torch.empty(*shape, device=DEVICE).uniform_()
 
 
 def set_device(device):

@@ -51,19 +51,39 @@ def decoder_state(gen):
 
 
 def run(B, size, Nc, Nf, seed, origin="center+head", device="cpu", grad=True, keep_masks=True, loss_seed=5,
-        inputs=None, dtype=torch.float32):
-    """``dtype=torch.float64`` runs the same unmodified code with torch's default dtype switched to double (so every
+        inputs=None, dtype=torch.float32, allow_tf32=False,
+        force_draws=None):
+    """``allow_tf32``: torch's cuDNN convolutions default to TF32 on Ampere+ (``torch.backends.cudnn.allow_tf32`` is True
+    out of the box, in the reference's torch 1.10 as in 2.11), so ON A GPU the reference's grouped ``conv1d`` decoder
+    (custom_stylegan2/net.py:250) runs at ~1e-3 relative precision "as shipped".  Parity is adjudicated against the
+    same code with that switch off (true fp32); ``allow_tf32=True`` reproduces the stock behaviour for the record.
+    ``force_draws=(idx, jitter)`` pins the fine pass's multinomial indices and jitter (e.g. to those of an fp64 run, so
+    that the fp32 and the fp64 evaluation of the reference can be compared sample for sample).
+    ``dtype=torch.float64`` runs the same unmodified code with torch's default dtype switched to double (so every
     tensor the reference creates itself is fp64 too): the "fp64-cast reference" of SURVEY 8c(2), free of the fp32
     x-remap noise of its batched gather (H1) -- the adjudicator when fp32 reference and fp32 kernels disagree at 1e-4."""
+    if inputs is None:          # generated under the fp32 default: the same numbers whatever ``dtype`` the run uses
+        P = 24 if origin == "center+head" else 23
+        inputs = (S.make_inputs(B, size, seed=seed), S.make_triplane(B, num_part=P, seed=seed), S.make_latent(B, seed=seed))
+    # the random-init generator too is drawn under the fp32 default (an fp64 default would draw different weights)
+    H.set_device("cpu")
+    gen = H.build_generator(size, S.canonical_pose(), S.SMPL_PARENTS, seed=seed, Nc=Nc, Nf=Nf, origin_location=origin)
+    with torch.no_grad():
+        for layer in gen.nerf.mlp.layers:       # non-trivial biases so the bias path is exercised
+            layer.bias.normal_(0, 0.3)
     if dtype == torch.float64:
         torch.set_default_dtype(torch.float64)
+    keep = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = bool(allow_tf32)     # the stock default is True
+    torch.backends.cuda.matmul.allow_tf32 = False          # the stock default (torch >= 1.12)
     try:
-        return _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inputs, dtype)
+        return _run(gen, B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inputs, dtype, force_draws)
     finally:
         torch.set_default_dtype(torch.float32)
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = keep
 
 
-def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inputs, dtype):
+def _run(gen, B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inputs, dtype, force_draws=None):
     """-> dict with the reference's outputs (on ``device``):
     color (B,3,size,size), mask (B,size,size), disparity (B,n_all) [already x coordinate_scale], fine_weights
     (B,n,Nf-1), fine_depth (B,n,Nf), validity (B,n_all) bool, idx (B*n,Nf) / jitter (B*n,Nf) = the fine pass's draws,
@@ -71,17 +91,9 @@ def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inp
     ``grad``: d_tri_plane (B,C,256,256), param_grads {state-dict name: grad}, loss."""
     H.set_device(device)
     dev = torch.device(device)
-    gen = H.build_generator(size, S.canonical_pose(), S.SMPL_PARENTS, seed=seed, Nc=Nc, Nf=Nf, origin_location=origin)
     P = gen.nerf.num_bone
-    if inputs is None:
-        inp = S.make_inputs(B, size, seed=seed)
-        tp = S.make_triplane(B, num_part=P, seed=seed)
-        z = S.make_latent(B, seed=seed)
-    else:
-        inp, tp, z = inputs
-    with torch.no_grad():
-        for layer in gen.nerf.mlp.layers:       # non-trivial biases so the bias path is exercised
-            layer.bias.normal_(0, 0.3)
+    inp, tp, z = inputs
+    assert tp.shape[1] == (32 + P) * 3
     gen = gen.to(dev).to(dtype).eval()          # eval: temporal_state keeps the intermediates; arithmetic unchanged
     nerf = gen.nerf
     tp_d = tp.detach().to(dev).to(dtype).clone().requires_grad_(grad)
@@ -98,6 +110,8 @@ def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inp
 
     def recording_multinomial(w, n, replacement=False):
         idx = real_multinomial(w, n, replacement=replacement)
+        if force_draws is not None:
+            idx = force_draws[0].to(idx.device).reshape(idx.shape)
         draws["idx"] = idx.clone()
         draws["weights"] = w.detach().clone()
         draws["state"] = torch.cuda.get_rng_state(dev) if dev.type == "cuda" else torch.get_rng_state()
@@ -105,6 +119,7 @@ def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inp
 
     torch.manual_seed(seed + 1)
     torch.multinomial = recording_multinomial
+    H.FORCED_JITTER = None if force_draws is None else force_draws[1].to(dtype)
     c = lambda k: inp[k].to(dev).to(dtype)
     try:
         with torch.set_grad_enabled(grad):
@@ -112,6 +127,7 @@ def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inp
                                          c("inv_intrinsics"), return_disparity=True)
     finally:
         torch.multinomial = real_multinomial
+        H.FORCED_JITTER = None
     fw = nerf.buffers_tensors["fine_weights"][:, 0]
     fd = nerf.buffers_tensors["fine_depth"][:, 0]
     n = fw.shape[1]
@@ -126,6 +142,8 @@ def _run(B, size, Nc, Nf, seed, origin, device, grad, keep_masks, loss_seed, inp
         torch.set_rng_state(draws["state"])
         jitter = torch.empty(B, 1, n, Nf).uniform_().reshape(B * n, Nf)
         torch.set_rng_state(keep)
+    if force_draws is not None:
+        jitter = force_draws[1].to(dev).reshape(B * n, Nf)
     ts = nerf.temporal_state
     out = dict(color=color.detach(), mask=mask.detach(), disparity=disparity.detach(), fine_weights=fw.detach(),
                fine_depth=fd.detach(), idx=draws["idx"], jitter=jitter, coarse_weights_blurred=draws["weights"],

@@ -31,7 +31,8 @@ def test_philox_bins_follow_the_multinomial_law():
                           torch.ones(R, Nf, device="cuda", dtype=torch.float64))
         frac.append(bins * Nc - torch.floor(bins * Nc))          # the jitter inside the bin
         assert torch.all(bins[:, 1:] >= bins[:, :-1]), "bins must come out sorted"
-        assert torch.equal(torch.floor(bins * Nc).long().clamp(max=Nc - 1).sort(dim=1)[0], idx.long().sort(dim=1)[0])
+        # bins = (idx + jitter) / Nc (rendering.py:195-196): each sorted bin lies in its index's cell (up to rounding)
+        assert ((bins * Nc - idx.sort(dim=1)[0].float() - 0.5).abs() <= 0.5 + 1e-3).all()
     dof = R * (Nc - 1)
     sd = (2 * dof) ** 0.5
     s_ours, s_ctrl = _chi2(ours, prob).sum().item(), _chi2(ctrl, prob).sum().item()
