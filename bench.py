@@ -182,7 +182,7 @@ def step_device(w, step_idx, timer=None, world=None):
             scene.ref, p(dmin), p(dmax), p(direction), p(bins), p(pts), p(feat), pairs.ref, n, NF, p(w["g_color"]), p(w["g_mask"]),
             None, None,
             p(d_feat), d_tp[:, 96:].data_ptr(), d_tp.stride(0), p(dw[0]), p(dw[1]), p(dw[2]), p(db[0]), p(db[1]), p(db[2]),
-            ops.stream_ptr()))
+            0.0, ops.stream_ptr()))
     timed("fine_bwd", bwd)
     timed("unpack", lambda: ops.unpack_plane_grads(d_feat, d_tp, accumulate=False))
     w["last"] = (color, mask, d_tp, dw, bins, dmin, dmax, direction)

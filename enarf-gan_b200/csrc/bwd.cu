@@ -48,6 +48,7 @@ struct BwdArgs {
     float *d_w1, *d_w2, *d_w3, *d_b1, *d_b2, *d_b3;
     int rays_per_tile, tiles_per_sample;
     int* tile_counter;
+    float ert_eps;            // > 0: the forward ran with early ray termination (group-major pair order, dropped samples)
 };
 
 struct __align__(16) BwdSmem {
@@ -355,7 +356,13 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         // a ray too); that sample then flows through with a zero upstream gradient.  Otherwise it is skipped outright.
         TileGeom geom = a.g;
         geom.skip_last = tb < 0;
-        tile_points<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
+        tile_masks<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
+        {
+            // the forward's list: point order, or with early termination group-major without the samples it dropped
+            const bool ert = a.ert_eps > 0.f;
+            const int K = ert ? ERT_GROUP : S;
+            tile_compact(s.t, rays, S, K, 0, (S + K - 1) / K, 0xffffffffu, ert ? s.pg : nullptr, tid);
+        }
         const int n_active = s.t.n_active;
         PHASE(1);   // tile_points
 
@@ -372,7 +379,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 const int j = base + lane;
                 const bool ok = j < M;
                 const float4 sv = ok ? *reinterpret_cast<const float4*>(go + j * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
-                const float dd = ok ? sv.w * (dep[j + 1] - dep[j]) : 0.f;
+                const float dd = ok ? fmaxf(sv.w, 0.f) * (dep[j + 1] - dep[j]) : 0.f;   // dropped sample: sigma < 0
                 float incl = dd;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
@@ -604,7 +611,7 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
                                      const float* g_color, const float* g_mask, const float* g_disparity,
                                      const float* g_fine_weights, float* d_feat, float* d_prob,
                                      int64_t d_prob_batch_stride, float* d_w1, float* d_w2, float* d_w3, float* d_b1,
-                                     float* d_b2, float* d_b3, void* stream) {
+                                     float* d_b2, float* d_b3, float ert_eps, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_bwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && point_saved, ENARF_ERR_INVALID_ARG,
@@ -645,6 +652,7 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     a.d_b1 = d_b1;
     a.d_b2 = d_b2;
     a.d_b3 = d_b3;
+    a.ert_eps = ert_eps;
     a.rays_per_tile = max(1, min(MAX_RAYS, TP_MAX / Nf));
     a.tiles_per_sample = (n + a.rays_per_tile - 1) / a.rays_per_tile;
     const int total = scene->B * a.tiles_per_sample;

@@ -54,7 +54,15 @@ struct RenderArgs {
     float* q_density;
     float* q_color;
     uint32_t* q_mask;
+    // early ray termination (fine pass): threshold on the prefix transmittance (0 = off), the coarse pass's count of
+    // opaque rays (rounds are only worth their barriers when there are some; NULL = always), statistics out
+    float ert_eps;
+    const int* ert_hint;
+    int ert_min_count;
+    int* ert_stats;         // [0] += active points evaluated, [1] += active points skipped
+    int* opaque_rays;       // coarse pass: += rays whose coarse transmittance ends below OPAQUE_T
 };
+#define OPAQUE_T 1e-2f
 
 static_assert((32 * XSW + RECW * REC) >= 32 * 64, "the slab holds the 32 x 64 layer-1 activations");
 struct __align__(16) WarpSlab {
@@ -104,37 +112,63 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             load_decoder_mma(s.dec, sc, b, tid, NT);
             cur_b = b;
         }
-        if (tid == 0) s.t.pad_[0] = 0;   // chunk counter of this tile
-        tile_points<MODE>(s.t, *reinterpret_cast<RecSmem*>(&s.u), s.part, a.g, sc.P, b, ray0, rays, tid);
-        const int n_active = s.t.n_active;
-        if (MODE == MODE_FINE && a.ck.rec) {   // hand this tile its slice of the pair checkpoint
-            if (tid == 0) {
-                const int np_tile = s.t.pref[n_active];
-                // once the checkpoint is full the cursor is left alone, so it cannot wrap however many tiles follow
-                int base = -1;
-                if (*reinterpret_cast<volatile int*>(a.ck.cursor) <= a.ck.capacity) {
-                    base = atomicAdd(a.ck.cursor, np_tile);
-                    if ((long long)base + np_tile > a.ck.capacity) base = -1;
-                }
-                a.ck.tile_base[tile] = base;
-                s.t.pad_[1] = base;
-            }
-            __syncthreads();
+        const bool ert = MODE != MODE_QUERY && a.ert_eps > 0.f;
+        // sample groups are evaluated in separate rounds only when the coarse pass saw opaque rays
+        const int groups = ert ? (S + ERT_GROUP - 1) / ERT_GROUP : 1;
+        const int rounds = (ert && (!a.ert_hint || *a.ert_hint >= a.ert_min_count)) ? groups : 1;
+        tile_masks<MODE>(s.t, *reinterpret_cast<RecSmem*>(&s.u), s.part, a.g, sc.P, b, ray0, rays, tid);
+        if (tid == 0) {
+            s.t.alive = 0xffffffffu;
+            s.t.pad_[0] = 0;   // chunk counter of this round
         }
+        if (ert && tid < MAX_RAYS) s.t.carry[tid] = 0.f;
         if (MODE == MODE_QUERY && a.q_mask)
             for (int i = tid; i < tp; i += NT) a.q_mask[(size_t)b * n + ray0 + i] = __float_as_uint(s.t.pm[i].w);
         float4* out = s.t.pm;
 
         FWD_PHASE(0);   // tile prologue: rays, phase 0/1, compaction, prefix
-        // ---- chunks of 32 active points, one warp each, no CTA barrier ---------------------------------
-        {
+        // ---- chunks of 32 active points, one warp each, no CTA barrier; with early termination on an opaque scene the
+        // sample groups go front to back in rounds, each followed by a partial composite that retires finished rays
+        int n_done = 0;
+        for (int rd = 0; rd < rounds; ++rd) {
+            // (round 0: every ray is alive -- s.t.alive was only just written by thread 0)
+            tile_compact(s.t, rays, S, ert ? ERT_GROUP : S, rounds == 1 ? 0 : rd, rounds == 1 ? groups : rd + 1,
+                         rd == 0 ? 0xffffffffu : s.t.alive, nullptr, tid);
+            const int n_active = s.t.n_active;
+            if (rd == 0 && MODE == MODE_FINE && a.ck.rec) {   // hand this tile its slice of the pair checkpoint
+                if (rounds > 1) {   // later rounds append to the list: size the slice for every active point of the tile
+                    int mine = 0;
+                    for (int i = tid; i < tp; i += NT) {
+                        const float w = s.t.pm[i].w;
+                        if (w != ERT_SENTINEL) mine += __popc(__float_as_uint(w));
+                    }
+#pragma unroll
+                    for (int o = 16; o; o >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, o);
+                    if (lane == 0) s.t.wsum[warp] = mine;
+                    __syncthreads();
+                }
+                if (tid == 0) {
+                    int np_tile = 0;
+                    if (rounds > 1) for (int w = 0; w < NWARP; ++w) np_tile += s.t.wsum[w];
+                    else np_tile = s.t.pref[n_active];
+                    // once the checkpoint is full the cursor is left alone, so it cannot wrap however many tiles follow
+                    int base = -1;
+                    if (*reinterpret_cast<volatile int*>(a.ck.cursor) <= a.ck.capacity) {
+                        base = atomicAdd(a.ck.cursor, np_tile);
+                        if ((long long)base + np_tile > a.ck.capacity) base = -1;
+                    }
+                    a.ck.tile_base[tile] = base;
+                    s.t.pad_[1] = base;
+                }
+                __syncthreads();
+            }
             WarpSlab& my = s.u.slab[warp];
             const int g = lane >> 2, t4 = lane & 3;
             for (;;) {
                 int c = 0;
                 if (lane == 0) c = atomicAdd(&s.t.pad_[0], 1);
                 c = __shfl_sync(0xffffffffu, c, 0);
-                const int a0 = 32 * c;
+                const int a0 = n_done + 32 * c;
                 if (a0 >= n_active) break;
                 const int np = min(32, n_active - a0);
                 const int tb = (MODE == MODE_FINE && a.ck.rec) ? s.t.pad_[1] : -1;
@@ -172,10 +206,34 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 }
                 FWD_PHASE(3);   // checkpoint row store + decoder + head
             }
+            __syncthreads();
+            if (rd + 1 < rounds) {
+                // optical depth of group rd's intervals, added to the ray's running total (exact prefix, sample order)
+                for (int r = warp; r < rays; r += NWARP) {
+                    const int j = rd * ERT_GROUP + lane;
+                    float dd = 0.f;
+                    if (lane < ERT_GROUP && j < S - 1) {
+                        const float* dep = s.t.depth + r * (S + 1);
+                        dd = fmaxf(out[r * S + j].w, 0.f) * (dep[j + 1] - dep[j]);
+                    }
+#pragma unroll
+                    for (int o = 8; o; o >>= 1) dd += __shfl_xor_sync(0xffffffffu, dd, o);
+                    if (lane == 0) {
+                        const float od = s.t.carry[r] + dd;
+                        s.t.carry[r] = od;
+                        if (expf(-od) < a.ert_eps) atomicAnd(&s.t.alive, ~(1u << r));
+                    }
+                }
+                if (tid == 0) s.t.pad_[0] = 0;
+                __syncthreads();
+            }
+            n_done = n_active;
         }
-        FWD_PHASE(6);   // failed chunk claim
-        __syncthreads();
-        FWD_PHASE(4);   // idle at the end of the tile's chunk phase
+        if (MODE != MODE_QUERY && a.ert_stats && tid == 0) {
+            atomicAdd(a.ert_stats, n_done);
+            if (s.t.skipped) atomicAdd(a.ert_stats + 1, s.t.skipped);
+        }
+        FWD_PHASE(4);   // failed chunk claims + idle at the end of the tile's chunk phase(s)
 
         // ---- outputs ---------------------------------------------------------------------------------
         if (MODE == MODE_QUERY) {
@@ -208,7 +266,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             for (int base = 0; base < M; base += 32) {
                 const int j = base + lane;
                 const bool ok = j < M;
-                const float sigma = ok ? po[j * 4 + 3] : 0.f;
+                const float sigma = ok ? fmaxf(po[j * 4 + 3], 0.f) : 0.f;   // (a dropped sample carries ERT_SENTINEL)
                 const float dd = ok ? sigma * (dep[j + 1] - dep[j]) : 0.f;
                 float incl = dd;
 #pragma unroll
@@ -234,6 +292,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 }
             }
             if (MODE == MODE_COARSE) {
+                if (a.opaque_rays && lane == 0 && expf(-carry) < OPAQUE_T) atomicAdd(a.opaque_rays, 1);
                 __syncwarp();
                 // (max(w[j-1],w[j]) + max(w[j],w[j+1]))/2 + 0.01, zero padded (rendering.py:187-190)
                 for (int j = lane; j < S; j += 32) {
@@ -315,7 +374,7 @@ extern "C" int enarf_fine_tiles_per_sample(int n, int Nf) {
 
 extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                    const float* ray_dir, int n, int Nc, float* weights_out, float* density_out,
-                                   void* stream) {
+                                   int* opaque_rays, float ert_eps, const int* ert_hint, int* ert_stats, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_coarse");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && weights_out, ENARF_ERR_INVALID_ARG,
@@ -333,13 +392,20 @@ extern "C" int enarf_render_coarse(const enarf_scene_t* scene, const float* dept
     a.tiles_per_sample = (n + a.rays_per_tile - 1) / a.rays_per_tile;
     a.weights_out = weights_out;
     a.density_out = density_out;
+    a.opaque_rays = opaque_rays;
+    ENARF_REQUIRE(ert_eps >= 0.f && ert_eps < 1.f, ENARF_ERR_INVALID_ARG, "enarf_render_coarse: ert_eps must be in [0, 1)");
+    a.ert_eps = ert_eps;
+    a.ert_hint = ert_hint;
+    a.ert_min_count = max(1, (int)(((long long)scene->B * n) / 64));
+    a.ert_stats = ert_stats;
     return launch_render<MODE_COARSE>(a, "enarf_render_coarse", (cudaStream_t)stream);
 }
 
 extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                                      const float* ray_dir, const float* bins, int n, int Nf, float* color,
                                      float* mask, float* disparity, float* fine_weights, float* fine_depth,
-                                     float* point_out, float* feat_out, const enarf_pair_ckpt_t* pair_ckpt, void* stream) {
+                                     float* point_out, float* feat_out, const enarf_pair_ckpt_t* pair_ckpt, float ert_eps,
+                                     const int* ert_hint, int* ert_stats, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_fwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && color && mask && disparity && fine_weights && fine_depth,
@@ -365,6 +431,13 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
     a.fine_weights = fine_weights;
     a.point_out = point_out;
     a.feat_out = feat_out;
+    ENARF_REQUIRE(ert_eps >= 0.f && ert_eps < 1.f, ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: ert_eps must be in [0, 1)");
+    ENARF_REQUIRE(!(ert_eps > 0.f) || point_out, ENARF_ERR_INVALID_ARG,
+                  "enarf_render_fine_fwd: early termination records the dropped samples in point_out");
+    a.ert_eps = ert_eps;
+    a.ert_hint = ert_hint;
+    a.ert_min_count = max(1, (int)(((long long)scene->B * n) / 64));   // rounds pay once ~1.5 % of the rays are opaque
+    a.ert_stats = ert_stats;
     if (pair_ckpt) {
         ENARF_REQUIRE(pair_ckpt->rec && pair_ckpt->feat && pair_ckpt->tile_base && pair_ckpt->cursor && pair_ckpt->capacity > 0 &&
                           ((uintptr_t)pair_ckpt->rec & 15) == 0 && ((uintptr_t)pair_ckpt->feat & 15) == 0,

@@ -65,11 +65,22 @@ struct __align__(16) TileSmem {
     uint16_t list[TP_MAX];
     uint16_t pref[TP_MAX + 8];
     uint32_t act[TP_MAX / 32];         // bit i%32 of word i/32: point i is inside at least one part
+    uint32_t sel[TP_MAX / 32];         // compaction scratch: the same bits in the order the list is built in
+    float carry[MAX_RAYS];             // early ray termination: optical depth of the sample groups composited so far
+    uint32_t alive;                    // early ray termination: bit r set = ray r of the tile is still transparent
+    int skipped;                       // active points dropped because their ray had terminated (statistics)
     int wsum[NWARP];
     int n_active;
     int tile;
     int pad_[2];
 };
+
+// Early ray termination (north_star step (e)): the samples of a ray are evaluated front to back in groups
+// of ERT_GROUP; once the exact prefix transmittance of a ray has dropped below the caller's threshold its remaining
+// samples are not evaluated and composite with density 0.  A dropped sample is marked by a negative density in
+// the saved (r,g,b,sigma) record, which is how the backward learns to leave it out too.
+#define ERT_GROUP 16
+#define ERT_SENTINEL (-1.0f)
 
 union __align__(16) RecSmem {
     float rec[PB * REC];
@@ -103,13 +114,17 @@ struct TileGeom {
     int skip_last;       // backward: the last sample of a ray only closes the last interval, no gradient
 };
 
-// Loads the tile's rays, clips them against the parts and fills pm / depth / list / pref.  Ends synchronised.
+// Loads the tile's rays, clips them against the parts and fills pm / depth / act (the part masks of every point);
+// resets the active list.  Ends synchronised.
 template <int MODE>
-__device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float* s_part, const TileGeom& g, int P,
+__device__ __forceinline__ void tile_masks(TileSmem& t, RecSmem& r, const float* s_part, const TileGeom& g, int P,
                                             int b, int ray0, int rays, int tid) {
     const int lane = tid & 31, warp = tid >> 5;
     const int S = g.S, n = g.n, tp = rays * S;
-    if (tid == 0) t.n_active = 0;
+    if (tid == 0) {
+        t.n_active = 0;
+        t.skipped = 0;
+    }
     if (MODE != TILE_QUERY && tid < rays) {
         const size_t o = (size_t)b * n + ray0 + tid;
         const float* d = g.dir + (size_t)b * 3 * n + ray0 + tid;
@@ -190,21 +205,72 @@ __device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float
         if (lane == 0) t.act[i >> 5] = bal;
     }
     __syncthreads();
-    // compaction in point order (deterministic: the forward and the backward of a tile see the same list, and a
-    // chunk's points are consecutive along their rays): block b of 32 points starts at the popcount of the blocks before
-    for (int i = tid; i < ((tp + 31) & ~31); i += NT) {
-        const uint32_t bal = t.act[i >> 5];
-        int base = 0;
-        for (int k = 0; k < (i >> 5); ++k) base += __popc(t.act[k]);
-        if ((bal >> lane) & 1) t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)i;
-        if (i + 32 >= ((tp + 31) & ~31) && lane == 0) t.n_active = base + __popc(bal);   // the last block closes the count
+}
+
+// ---- compaction -----------------------------------------------------------------------------------------
+// Appends to t.list the active points of the sample groups [g0, g1) -- group g = samples [g*K, min(S, (g+1)*K)) of
+// every ray -- in (group, ray, sample) order, and extends the pair prefix t.pref over them.  With K >= S there is one
+// group and the order is plain point order.  Deterministic: the forward and the backward of a tile build the same
+// list, and a chunk's points are consecutive along their rays.  Only rays whose bit is set in `alive` contribute; an
+// active point of a dead ray is marked ERT_SENTINEL instead (forward).  `saved` (backward): the forward's
+// (r,g,b,sigma) records -- points the forward dropped (sigma < 0) are left out.  Call with t.n_active = 0 for the
+// first range of a tile.  Ends synchronised.
+__device__ __forceinline__ void tile_compact(TileSmem& t, int rays, int S, int K, int g0, int g1, uint32_t alive,
+                                             const float4* saved, int tid) {
+    const int lane = tid & 31, warp = tid >> 5;
+    const int s0 = g0 * K, s1 = min(S, g1 * K);
+    const int cnt = rays * (s1 - s0), cnt32 = (cnt + 31) & ~31;
+    const int n0 = t.n_active;
+    // position q of the range -> point index i = ray * S + sample
+    auto point_of = [&](int q, int& rr) {
+        const int g = q / (rays * K);                 // every group but the last holds rays*K positions
+        const int within = q - g * rays * K, base = (g0 + g) * K;
+        const int kg = min(K, S - base);
+        rr = within / kg;
+        return rr * S + base + (within - rr * kg);
+    };
+    const bool all_alive = alive == 0xffffffffu;      // (point queries pass > 32 "rays")
+    // plain point order over the whole tile with nothing to filter: the part-mask bitmap already is the selection
+    const bool direct = K >= S && all_alive && !saved;
+    if (!direct) {
+        int dropped = 0;
+        for (int q = tid; q < cnt32; q += NT) {
+            bool on = false;
+            if (q < cnt) {
+                int rr;
+                const int i = point_of(q, rr);
+                on = (t.act[i >> 5] >> (i & 31)) & 1;
+                if (on && saved && saved[i].w < 0.f) on = false;
+                if (on && !all_alive && !((alive >> rr) & 1)) {
+                    on = false;
+                    t.pm[i] = make_float4(0.f, 0.f, 0.f, ERT_SENTINEL);
+                    ++dropped;
+                }
+            }
+            const uint32_t bal = __ballot_sync(0xffffffffu, on);
+            if (lane == 0) t.sel[q >> 5] = bal;
+        }
+        if (dropped) atomicAdd(&t.skipped, dropped);
+        __syncthreads();
+    }
+    const uint32_t* bits = direct ? t.act : t.sel;
+    for (int q = tid; q < cnt32; q += NT) {
+        const uint32_t bal = bits[q >> 5];
+        int base = n0;
+        for (int k = 0; k < (q >> 5); ++k) base += __popc(bits[k]);
+        if ((bal >> lane) & 1) {
+            int rr;
+            t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)(direct ? q : point_of(q, rr));
+        }
+        if (q + 32 >= cnt32 && lane == 0) t.n_active = base + __popc(bal);   // the last block closes the count
     }
     __syncthreads();
-    // exclusive prefix of pairs-per-point over the active list (2 entries per thread)
-    const int na = t.n_active;
+    // exclusive prefix of pairs-per-point over the new list entries (2 entries per thread)
+    const int na = t.n_active - n0;
+    const int p_base = n0 ? t.pref[n0] : 0;
     const int i0 = 2 * tid;
-    const int c0 = i0 < na ? __popc(__float_as_uint(t.pm[t.list[i0]].w)) : 0;
-    const int c1 = i0 + 1 < na ? __popc(__float_as_uint(t.pm[t.list[i0 + 1]].w)) : 0;
+    const int c0 = i0 < na ? __popc(__float_as_uint(t.pm[t.list[n0 + i0]].w)) : 0;
+    const int c1 = i0 + 1 < na ? __popc(__float_as_uint(t.pm[t.list[n0 + i0 + 1]].w)) : 0;
     const int s2 = c0 + c1;
     int incl = s2;
 #pragma unroll
@@ -214,13 +280,21 @@ __device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float
     }
     if (lane == 31) t.wsum[warp] = incl;
     __syncthreads();
-    int base = 0;
+    int base = p_base;
     for (int w = 0; w < warp; ++w) base += t.wsum[w];
     const int excl = base + incl - s2;
-    if (i0 <= na) t.pref[i0] = (uint16_t)excl;
-    if (i0 + 1 <= na) t.pref[i0 + 1] = (uint16_t)(excl + c0);
-    if (i0 + 2 == na && tid == NT - 1) t.pref[na] = (uint16_t)(excl + s2);   // na == 2*NT: nobody owns pref[na]
+    if (i0 <= na) t.pref[n0 + i0] = (uint16_t)excl;
+    if (i0 + 1 <= na) t.pref[n0 + i0 + 1] = (uint16_t)(excl + c0);
+    if (i0 + 2 == na && tid == NT - 1) t.pref[n0 + na] = (uint16_t)(excl + s2);   // na == 2*NT: nobody owns pref[na]
     __syncthreads();
+}
+
+// tile_masks + one compaction of every point in point order: the geometry every kernel without early termination uses
+template <int MODE>
+__device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float* s_part, const TileGeom& g, int P,
+                                            int b, int ray0, int rays, int tid) {
+    tile_masks<MODE>(t, r, s_part, g, P, b, ray0, rays, tid);
+    tile_compact(t, rays, g.S, g.S, 0, 1, 0xffffffffu, nullptr, tid);
 }
 
 // End (exclusive) of the chunk starting at active index a: at most CH points and PB pairs.

@@ -111,6 +111,9 @@ class TriPlaneNARF(nn.Module):
         self.plane_dtype = plane_dtype
         self.rng_mode = "torch"      # "torch": the reference's multinomial/uniform_ stream; "philox": in-kernel
         self.rng_seed = 0
+        # early ray termination of the fine pass (north_star step (e)): 0 = off = the reference's exact semantics;
+        # e.g. 1e-6 stops a ray once its transmittance is below that (outputs move by < 1e-6), see rendering.render_rays
+        self.ert_eps = float(_cfg(config, "ert_eps", 0.0) or 0.0)
         self.temporal_state = {}
         self.buffers_tensors = {}
         self.deformation_field = False

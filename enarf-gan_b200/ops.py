@@ -173,13 +173,17 @@ def depth_range(image_coord, inv_K, pose, nearfar=None):
     return dmin, dmax, direction, valid.bool()
 
 
-def render_coarse(scene, dmin, dmax, direction, Nc, want_density=False):
-    """-> blurred coarse weights (B,n,Nc) [, density (B,n,Nc)]."""
+def render_coarse(scene, dmin, dmax, direction, Nc, want_density=False, opaque_rays=None, ert_eps=0.0, ert_hint=None,
+                  ert_stats=None):
+    """-> blurred coarse weights (B,n,Nc) [, density (B,n,Nc)].  ``opaque_rays``: a zeroed int32 tensor of one element
+    that receives the number of rays the coarse pass found opaque (the early-termination hint of the fine pass).
+    ert_eps / ert_hint / ert_stats: early termination of the coarse samples (see render_rays)."""
     B, n = dmin.shape
     wb = torch.empty(B, n, Nc, device=dmin.device)
     den = torch.empty(B, n, Nc, device=dmin.device) if want_density else None
     check(lib().enarf_render_coarse(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), n, Nc, ptr(wb),
-                                    ptr(den, allow_none=True), stream_ptr()))
+                                    ptr(den, allow_none=True), ptr(opaque_rays, torch.int32, True), float(ert_eps),
+                                    ptr(ert_hint, torch.int32, True), ptr(ert_stats, torch.int32, True), stream_ptr()))
     return (wb, den) if want_density else wb
 
 
@@ -245,7 +249,8 @@ class PairCheckpoint:
         return self
 
 
-def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False, want_pairs=False):
+def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False, want_pairs=False,
+                     ert_eps=0.0, ert_hint=None, ert_stats=None):
     """-> color, mask, disp, fine_weights, fine_depth [, points (B,n,Nf,4)] [, feat (B,n,Nf,32) checkpoint: only
     the rows of samples inside a part are written] [, PairCheckpoint]."""
     B, n, Nf = bins.shape
@@ -255,12 +260,13 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     disp = torch.empty(B, n, device=dev)
     fw = torch.empty(B, n, Nf - 1, device=dev)
     fd = torch.empty(B, n, Nf, device=dev)
-    pts = torch.empty(B, n, Nf, 4, device=dev) if want_points else None
+    pts = torch.empty(B, n, Nf, 4, device=dev) if (want_points or ert_eps > 0) else None
     feat = torch.empty(B, n, Nf, FEAT_DIM, device=dev) if want_feat else None
     pairs = PairCheckpoint(B, n, Nf, dev) if want_pairs else None
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
                                       ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True),
-                                      ptr(feat, allow_none=True), pairs.ref if pairs else None, stream_ptr()))
+                                      ptr(feat, allow_none=True), pairs.ref if pairs else None, float(ert_eps),
+                                      ptr(ert_hint, torch.int32, True), ptr(ert_stats, torch.int32, True), stream_ptr()))
     out = (color, mask, disp, fw, fd)
     if want_points:
         out += (pts,)
@@ -271,12 +277,14 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     return out
 
 
-def _fine_forward(ctx, scene, dmin, dmax, direction, bins):
-    """Forward of both autograd Functions: run the fused pass with the checkpoints a backward wants and stash them."""
+def _fine_forward(ctx, scene, dmin, dmax, direction, bins, ert):
+    """Forward of both autograd Functions: run the fused pass with the checkpoints a backward wants and stash them.
+    ``ert`` = (ert_eps, ert_hint, ert_stats) of the early ray termination."""
     pairs_on = SAVE_FEATURES and PAIR_CKPT
     out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
-                           want_pairs=pairs_on)
+                           want_pairs=pairs_on, ert_eps=ert[0], ert_hint=ert[1], ert_stats=ert[2])
     ctx.scene = scene
+    ctx.ert_eps = float(ert[0])
     saved = [dmin, dmax, direction, bins, out[5]]
     if SAVE_FEATURES:
         saved.append(out[6])
@@ -305,7 +313,7 @@ def _fine_backward(ctx, grads, d_feat, d_prob, d_prob_stride):
         pairs.ref if pairs else None, n, Nf,
         ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
         ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_prob_stride,
-        ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), stream_ptr()))
+        ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), ctx.ert_eps, stream_ptr()))
     return (dw[0], dw[1], dw[2], db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)),
             db[2].reshape(ctx_shape(scene, 2)))
 
@@ -316,9 +324,9 @@ class RenderFine(torch.autograd.Function):
     reference (rendering.py:216-217)."""
 
     @staticmethod
-    def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3):
+    def forward(ctx, scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3, ert=(0.0, None, None)):
         ctx.tp_shape = tri_plane.shape
-        return _fine_forward(ctx, scene, dmin, dmax, direction, bins)
+        return _fine_forward(ctx, scene, dmin, dmax, direction, bins, ert)
 
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
@@ -344,7 +352,7 @@ class RenderFine(torch.autograd.Function):
         dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_prob, stride)
         if need_tp:
             unpack_plane_grads(d_feat, d_tp, accumulate=False)
-        return (None, None, None, None, None, d_tp) + dec
+        return (None, None, None, None, None, d_tp) + dec + (None,)
 
 
 class RenderFinePlanes(torch.autograd.Function):
@@ -353,9 +361,10 @@ class RenderFinePlanes(torch.autograd.Function):
     accumulates it (no unpack), d_prob summed over the batch when the planes are shared."""
 
     @staticmethod
-    def forward(ctx, scene, dmin, dmax, direction, bins, feat_planes, prob_planes, w1, w2, w3, b1, b2, b3):
+    def forward(ctx, scene, dmin, dmax, direction, bins, feat_planes, prob_planes, w1, w2, w3, b1, b2, b3,
+                ert=(0.0, None, None)):
         ctx.prob_shape = prob_planes.shape
-        return _fine_forward(ctx, scene, dmin, dmax, direction, bins)
+        return _fine_forward(ctx, scene, dmin, dmax, direction, bins, ert)
 
     @staticmethod
     def backward(ctx, g_color, g_mask, g_disp, g_fw, _g_fd, _g_pts):
@@ -366,24 +375,30 @@ class RenderFinePlanes(torch.autograd.Function):
         stride = 0 if ctx.prob_shape[0] == 1 else d_prob.stride(0)
         dec = _fine_backward(ctx, (g_color, g_mask, g_disp, g_fw), d_feat, d_prob, stride)
         return (None, None, None, None, None, d_feat if ctx.needs_input_grad[5] else None,
-                d_prob if ctx.needs_input_grad[6] else None) + dec
+                d_prob if ctx.needs_input_grad[6] else None) + dec + (None,)
 
 
 def ctx_shape(scene, i):
     return scene.b_shapes[i] if hasattr(scene, "b_shapes") else scene.b[i].shape
 
 
-def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None, want_points=None):
+def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None, want_points=None, ert_eps=0.0,
+                ert_hint=None, ert_stats=None):
     """-> color (B,3,n), mask (B,n), disparity (B,n), fine_weights (B,n,Nf-1), fine_depth (B,n,Nf)
     [, points (B,n,Nf,4) = per-sample (r,g,b,sigma) when ``want_points`` is given (None/False/True)].
     Pass the autograd-tracked ``tri_plane`` and ``decoder`` tensors to get gradients."""
     if tri_plane is None or not torch.is_grad_enabled():
-        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=bool(want_points))
+        out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=bool(want_points), ert_eps=ert_eps,
+                               ert_hint=ert_hint, ert_stats=ert_stats)
+        if ert_eps > 0 and not want_points:
+            out = out[:5]                       # the point records were only needed to mark the dropped samples
         return out if want_points is None or want_points else out + (None,)
     (w1, b1), (w2, b2), (w3, b3) = decoder
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
     if isinstance(tri_plane, (tuple, list)):        # (feat_planes channels-last, prob_planes NCHW)
-        out = RenderFinePlanes.apply(scene, dmin, dmax, direction, bins, tri_plane[0], tri_plane[1], w1, w2, w3, b1, b2, b3)
+        out = RenderFinePlanes.apply(scene, dmin, dmax, direction, bins, tri_plane[0], tri_plane[1], w1, w2, w3, b1, b2, b3,
+                                     (ert_eps, ert_hint, ert_stats))
         return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
-    out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3)
+    out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3,
+                           (ert_eps, ert_hint, ert_stats))
     return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))

@@ -105,10 +105,15 @@ int enarf_depth_range(const float* image_coord, const float* inv_K, const float*
 /* Limits of the fused passes below: 2 <= Nc, Nf <= 512 samples per ray, P <= 32 parts, H, W >= 2
  * (ENARF_ERR_UNSUPPORTED / ENARF_ERR_INVALID_ARG otherwise). */
 /* Coarse pass (rendering.py:119-190 + narf.py:176-275, no gradient): Nc stratified mid-points per ray ->
- * density -> alpha weights -> max-blur + 0.01.  weights_out (B,n,Nc); density_out (B,n,Nc) optional (NULL). */
+ * density -> alpha weights -> max-blur + 0.01.  weights_out (B,n,Nc); density_out (B,n,Nc) optional (NULL).
+ * opaque_rays (one int, optional): += the number of rays whose coarse transmittance ends below 1e-2 -- the hint
+ * enarf_render_fine_fwd uses to decide whether early-termination rounds are worth their barriers.
+ * ert_eps / ert_hint / ert_stats: early ray termination of the coarse samples themselves, as in
+ * enarf_render_fine_fwd below (a dropped coarse sample gets weight 0, i.e. the blurred weight's 0.01 floor; its true
+ * weight was below ert_eps); ert_hint is typically the PREVIOUS render call's opaque_rays. */
 int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                         const float* ray_dir, int n, int Nc, float* weights_out, float* density_out,
-                        void* stream);
+                        int* opaque_rays, float ert_eps, const int* ert_hint, int* ert_stats, void* stream);
 
 /* Hierarchical sampling (rendering.py:192-197): per ray draw Nf bins from the blurred coarse weights,
  * bins = idx/Nc + jitter/Nc, sorted ascending.  weights (R,Nc).  mode GIVEN: idx (R,Nf) int32 and jitter
@@ -138,22 +143,34 @@ int enarf_fine_tiles_per_sample(int n, int Nf);
  * (NULL to skip) -- it is what the backward consumes and what rendering.py:287 exposes as fine_density;
  * feat_out (B,n,Nf,32), optional (NULL to skip, the inference path): the gathered, part-weighted feature of
  * every sample that lies inside at least one part (other rows are left untouched) -- a checkpoint that lets the
- * backward skip its own gather; 16-byte aligned. */
+ * backward skip its own gather; 16-byte aligned.
+ * Early ray termination (north_star step (e); the reference composites every sample, rendering.py:307-335):
+ * ert_eps > 0 evaluates a ray's samples front to back in groups of 16 and stops once its exact prefix transmittance
+ * T = exp(-sum sigma*delta) is below ert_eps; the remaining samples get density 0 (their weights would sum to less
+ * than ert_eps: colour / mask / every fine_weight change by < ert_eps, disparity by < ert_eps / near) and are recorded
+ * in point_out with sigma = -1, from which the backward (same ert_eps) leaves them out as well.  point_out is then
+ * mandatory.  ert_hint (one int, optional): enarf_render_coarse's opaque_rays -- with fewer than B*n/64 opaque rays
+ * everything is evaluated in one round (no extra barriers); NULL = always in rounds.  ert_stats (two ints, optional):
+ * [0] += samples evaluated, [1] += samples skipped.  ert_eps = 0: off, the reference's exact semantics. */
 int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, int n, int Nf, float* color, float* mask,
                           float* disparity, float* fine_weights, float* fine_depth, float* point_out,
-                          float* feat_out, const enarf_pair_ckpt_t* pair_ckpt /* NULL = none */, void* stream);
+                          float* feat_out, const enarf_pair_ckpt_t* pair_ckpt /* NULL = none */, float ert_eps,
+                          const int* ert_hint, int* ert_stats, void* stream);
 
 /* Fine pass backward.  point_saved (B,n,Nf,4) is the forward's point_out; feat_saved (B,n,Nf,32) is the forward's
  * feat_out or NULL (the features are then gathered again); pair_ckpt requires feat_saved.  Upstream gradients (any may be NULL = zero):
  * g_color (B,3,n), g_mask (B,n), g_disparity (B,n), g_fine_weights (B,n,Nf-1).  Gradient buffers (caller
  * zero-initialises; results are ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as
- * scene->prob_planes, d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4). */
+ * scene->prob_planes, d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4).
+ * ert_eps: the value the forward was called with (> 0: the samples it dropped, sigma < 0 in point_saved, take no part
+ * and carry no gradient; the tile's pair order is the forward's). */
 int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, const float* point_saved, const float* feat_saved,
                           const enarf_pair_ckpt_t* pair_ckpt /* the forward's, or NULL */, int n, int Nf, const float* g_color, const float* g_mask, const float* g_disparity,
                           const float* g_fine_weights, float* d_feat, float* d_prob, int64_t d_prob_batch_stride,
-                          float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, void* stream);
+                          float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, float ert_eps,
+                          void* stream);
 
 /* Point query = calc_density_and_color_from_camera_coord_v2 (models/narf.py:176-211): points (B,3,N) in
  * the scaled camera frame -> density (B,1,N), color (B,3,N) (NULL to skip), part_mask (B,N) uint32 bit p =
