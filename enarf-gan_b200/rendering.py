@@ -131,7 +131,14 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
     planes_grad = any(t.requires_grad for t in tri_plane) if isinstance(tri_plane, (tuple, list)) \
         else tri_plane.requires_grad
     track = torch.is_grad_enabled() and (planes_grad or any(w.requires_grad for w, _ in decoder))
-    out = render_rays(scene, image_coord.reshape(B, 3, n_all), inv_intrinsics, Nc, Nf,
+    # sample-sharded batch (one process per GPU): near / far are batch-global in the reference (rendering.py:15-17), so
+    # the ranks exchange two floats; switch off with model.sync_near_far = False
+    nearfar = None
+    if getattr(model, "sync_near_far", True):
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            nearfar = global_near_far(scene.pose)
+    out = render_rays(scene, image_coord.reshape(B, 3, n_all), inv_intrinsics, Nc, Nf, nearfar=nearfar,
                       rng=getattr(model, "rng_mode", "torch"), seed=getattr(model, "rng_seed", 0),
                       idx=getattr(model, "rng_given", (None, None))[0],
                       jitter=getattr(model, "rng_given", (None, None))[1],
