@@ -37,6 +37,8 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=None,
                     help="samples per GPU (weak scaling); default: configs[2]'s global batch 32 split over the ranks")
     ap.add_argument("--global-batch", type=int, default=GLOBAL_BATCH)
+    ap.add_argument("--shard", default="balanced", choices=["balanced", "contiguous"],
+                    help="how the global batch is dealt to the ranks (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's eager path on this GPU")
     return ap.parse_args()
@@ -90,25 +92,36 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------------
 # workload
 # ----------------------------------------------------------------------------------------------------
+def batch_part_frames(global_batch):
+    """Scaled part frames of the whole synthetic batch (host data: 12 KB per sample)."""
+    from enarf_gan_b200 import hostmath, synthetic as S
+    per = [S.make_inputs(1, SIZE, seed=SEED + 17 * i) for i in range(global_batch)]
+    ptc, bl = torch.cat([q["pose_to_camera"] for q in per]), torch.cat([q["bone_length"] for q in per])
+    return hostmath.scaled_pose(hostmath.part_frames(ptc, bl, "center+head", S.SMPL_PARENTS)[0], 3.0)
+
+
 def local_batch(args, rank, world):
-    """(first sample, samples) of this rank: configs[2]'s fixed global batch split over the ranks (strong scaling),
-    or ``--batch`` samples on every rank (weak scaling)."""
+    """Indices (into the global batch) of this rank's samples: configs[2]'s fixed global batch dealt to the ranks
+    (strong scaling) -- by default balanced on a host-side cost proxy (rendering.balanced_shards), ``--shard contiguous``
+    for plain blocks -- or ``--batch`` samples of its own on every rank (weak scaling)."""
     if args.batch is not None:
-        return rank * args.batch, args.batch
-    from enarf_gan_b200.rendering import shard_samples
-    lo, hi = shard_samples(args.global_batch, rank, world)
-    return lo, hi - lo
+        return list(range(rank * args.batch, (rank + 1) * args.batch))
+    from enarf_gan_b200 import rendering
+    if args.shard == "balanced" and world > 1:
+        return rendering.balanced_shards(rendering.sample_cost_proxy(batch_part_frames(args.global_batch)), world)[rank]
+    lo, hi = rendering.shard_samples(args.global_batch, rank, world)
+    return list(range(lo, hi))
 
 
-def build_workload(first, B, device):
+def build_workload(samples, device, global_batch=None):
     """Synthetic batch resident in HBM: part frames, tri-planes (NCHW, as the reference produces them),
     per-sample decoder weights, rays, and fixed upstream gradients for the backward.  Sample g of the global batch is
     seeded by g alone, so the job renders the same 32 samples however many ranks share them."""
     from enarf_gan_b200 import hostmath, rendering, synthetic as S
-    seed = SEED
-    per = [S.make_inputs(1, SIZE, seed=SEED + 17 * (first + i)) for i in range(B)]
+    seed, B, first = SEED, len(samples), samples[0]
+    per = [S.make_inputs(1, SIZE, seed=SEED + 17 * i) for i in samples]
     inp = {k: torch.cat([q[k] for q in per], dim=0) for k in per[0]}
-    tp = torch.cat([S.make_triplane(1, num_part=PARTS, seed=SEED + 17 * (first + i)) for i in range(B)]).to(device)
+    tp = torch.cat([S.make_triplane(1, num_part=PARTS, seed=SEED + 17 * i) for i in samples]).to(device)
     frames, bl = hostmath.part_frames(inp["pose_to_camera"], inp["bone_length"], "center+head", S.SMPL_PARENTS)
     pose = hostmath.scaled_pose(frames, 3.0).to(device)
     cframes, clen = hostmath.canonical_part_frames(S.canonical_pose(), S.SMPL_PARENTS, "center+head")
@@ -121,7 +134,12 @@ def build_workload(first, B, device):
                                       torch.ones(cin), z)
         decoder.append((w.to(device), (0.3 * torch.randn(cout, generator=g)).to(device)))
     n = SIZE * SIZE
-    return dict(B=B, n=n, pose=pose, cscale=cscale, canon=cframes.to(device), tri_plane=tp, decoder=decoder,
+    # Batch-global near / far (rendering.py:15-17) need the root depths of the WHOLE batch: every rank is handed the
+    # full batch's part frames (12 KB per sample of host data) -- no collective on the render path
+    pose_all = pose
+    if global_batch is not None and global_batch != B:
+        pose_all = batch_part_frames(global_batch).to(device)
+    return dict(B=B, n=n, pose=pose, pose_all=pose_all, cscale=cscale, canon=cframes.to(device), tri_plane=tp, decoder=decoder,
                 inv_K=inp["inv_intrinsics"].to(device), img=rendering.pixel_grid(SIZE, SIZE, B, device),
                 g_color=torch.randn(B, 3, n, generator=g).to(device), g_mask=torch.randn(B, n, generator=g).to(device),
                 host=inp)
@@ -158,12 +176,7 @@ def step_device(w, step_idx, timer=None, world=None):
     B, n = w["B"], w["n"]
     dev = w["pose"].device
     scene = timed("repack", lambda: ops.SceneBuffers(w["pose"], w["cscale"], w["canon"], w["tri_plane"], w["decoder"]))
-    pose_all = w["pose"]
-    if world is not None:          # batch-global near/far (rendering.py:15-17) across the sharded batch: the
-        from enarf_gan_b200 import rendering   # path's only exchange, two all_reduces of one float (MIN, MAX)
-        nearfar = timed("near_far_allreduce", lambda: rendering.global_near_far(w["pose"]))
-    else:
-        nearfar = ops.near_far(pose_all)
+    nearfar = ops.near_far(w["pose_all"])      # batch-global (rendering.py:15-17): the full batch's frames are local
     dmin, dmax, direction, valid = timed("depth_range", lambda: ops.depth_range(w["img"], w["inv_K"], w["pose"], nearfar))
     wb = timed("coarse", lambda: ops.render_coarse(scene, dmin, dmax, direction, NC))
     bins = timed("fine_sample", lambda: ops.fine_sample(wb, NF, seed=step_idx))
@@ -233,6 +246,8 @@ def build_e2e(w, device):
     gen.register_canonical_pose(S.canonical_pose())
     gen = gen.to(device).train()
     gen.nerf.rng_mode = "philox"
+    from enarf_gan_b200 import ops
+    gen.nerf.batch_near_far = ops.near_far(w["pose_all"])     # batch-global near / far without a collective
     pin = lambda t: t.contiguous().pin_memory()
     host = {k: pin(w["host"][k]) for k in ("pose_to_camera", "pose_to_world", "bone_length", "inv_intrinsics")}
     host["z"] = pin(S.make_latent(w["B"], seed=SEED))
@@ -447,7 +462,7 @@ def base_line(args, value, ms, steps, world):
                                     f"{SIZE}x{SIZE} rays/sample, {NC}+{NF} samples/ray, P={PARTS} parts, global batch {gb} "
                                     + (f"= {args.batch} per GPU (weak)" if weak else f"sample-sharded over {world} GPU(s)")),
                        "global_batch": gb, "rays_per_step": gb * SIZE * SIZE,
-                       "points_per_ray": NC + NF, "parallelism": f"sample-sharded x{world}; only exchange: 2-float near/far all_reduce",
+                       "points_per_ray": NC + NF, "parallelism": f"sample-sharded x{world}, no data-path collective (every rank holds the batch's part frames)",
                        "l2": "inputs larger than L2 (tri-planes 44 MB/sample x batch, re-packed every step)"}}
 
 
@@ -466,9 +481,10 @@ def main():
         dist.init_process_group("nccl", device_id=device)
     from enarf_gan_b200 import _abi
     _abi.lib()
-    first, B = local_batch(args, rank, world)
+    samples = local_batch(args, rank, world)
+    B = len(samples)
     assert B > 0, "more ranks than samples: use render_entire_img_sharded (ray blocks) for B < G"
-    w = build_workload(first, B, device)
+    w = build_workload(samples, device, None if args.batch is not None else args.global_batch)
     wd = world if world > 1 else None
 
     def sync():
@@ -509,7 +525,7 @@ def main():
     clk = clocks.stop() if rank == 0 else None
     per_rank = None
     if world > 1:
-        mine = torch.tensor([ms, ms_e2e, kt.get("near_far_allreduce", 0.0)], device=device)
+        mine = torch.tensor([ms, ms_e2e, sum(kt.values())], device=device)
         allr = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(allr, mine)
         per_rank = [[round(v, 4) for v in t.tolist()] for t in allr]
@@ -528,10 +544,12 @@ def main():
     line["e2e"] = {"value": rays / (ms_e2e * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                    "ms_per_step": ms_e2e, "api": "TriNARFGenerator.forward + loss.backward (pinned host inputs)"}
     if per_rank is not None:
-        # [device ms, e2e ms, near/far all_reduce ms] of every rank: the spread is the load imbalance (each rank's samples
-        # have their own mean valid parts per point), the third column the only collective on the path
+        # [device ms, e2e ms, sum of kernel ms] of every rank: the spread is the load imbalance (each rank's samples have
+        # their own mean valid parts per point); there is no collective on the path
         line["per_rank_ms"] = per_rank
     line["samples_per_gpu"] = B
+    line["config"]["sharding"] = "weak: own samples per rank" if args.batch is not None else \
+        (f"{args.shard}" + (" (longest-processing-time-first on sum_parts 1/depth^2)" if args.shard == "balanced" else ""))
     line["pair_checkpoint_overflow_tiles"] = overflow
     # ---- roofline of the dominant kernel (rank 0's launches) ----
     (vc, ac), (vf, af) = mean_valid_parts(w)

@@ -52,10 +52,12 @@ class ModulatedConv1d(nn.Module):
         return torch.nn.functional.normalize(w, dim=-1)
 
 
-class _Noise(nn.Module):  # present in the reference's StyledConv even when unused; kept for key parity
+class _Noise(nn.Module):  # present in the reference's StyledConv even when unused; kept for checkpoint-key parity
     def __init__(self):
         super().__init__()
-        self.weight = nn.Parameter(torch.zeros(1))
+        # never used by the 1-D decoder (net.py:311: noise only for conv_2d), hence frozen: DDP's reducer would
+        # otherwise wait for a gradient that never comes
+        self.weight = nn.Parameter(torch.zeros(1), requires_grad=False)
 
 
 class StyledConv1d(nn.Module):
@@ -183,7 +185,9 @@ class TriPlaneNARF(nn.Module):
         """SceneBuffers for one render call + the autograd-tracked tensors behind it."""
         bone_length, z, z_rend = model_input["bone_length"], model_input["z"], model_input["z_rend"]
         tri_plane = model_input.get("tri_plane_feature")
-        decoder = self.mlp.effective(z_rend)
+        decoder = model_input.get("decoder")        # handed over by rendering.render_entire_img_sharded (owner's weights)
+        if decoder is None:
+            decoder = self.mlp.effective(z_rend)
         cscale = (self.canonical_bone_length[None, :, None] / bone_length / self.coordinate_scale)[:, :, 0]
         if self.deformation_field and tri_plane is None:
             planes = model_input.get("planes")
@@ -270,3 +274,14 @@ class TriPlaneNARF(nn.Module):
                 model_input["tri_plane_feature"] = self.compute_tri_plane_feature(z, bl)
         return rendering.render_entire_img(self, pose_to_camera, inv_intrinsics, camera_pose, render_size, Nc, Nf,
                                            semantic_map, use_normalized_intrinsics, no_grad, model_input, bbox=bbox)
+
+    def render_entire_img_sharded(self, pose_to_camera, inv_intrinsics, z, z_rend, bone_length, render_size=128, Nc=64,
+                                  Nf=128, no_grad=True, truncation_psi=1, bbox=None, group=None, owner=0):
+        """``render_entire_img`` with the one image's rays split over the ranks of ``group`` (fewer samples than GPUs);
+        with ``no_grad=False`` the gradients of every rank's ray block are summed onto ``owner``'s parameters
+        (rendering.render_entire_img_sharded)."""
+        model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
+        pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
+        return rendering.render_entire_img_sharded(self, pose_to_camera, inv_intrinsics, render_size=render_size, Nc=Nc,
+                                                   Nf=Nf, model_input=model_input, group=group, no_grad=no_grad,
+                                                   owner=owner, bbox=bbox)

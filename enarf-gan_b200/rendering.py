@@ -132,9 +132,9 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
         else tri_plane.requires_grad
     track = torch.is_grad_enabled() and (planes_grad or any(w.requires_grad for w, _ in decoder))
     # sample-sharded batch (one process per GPU): near / far are batch-global in the reference (rendering.py:15-17), so
-    # the ranks exchange two floats; switch off with model.sync_near_far = False
-    nearfar = None
-    if getattr(model, "sync_near_far", True):
+    # the ranks exchange two floats (switch off with model.sync_near_far = False), unless model.batch_near_far is set
+    nearfar = getattr(model, "batch_near_far", None)     # a caller that knows the whole batch's range hands it over
+    if nearfar is None and getattr(model, "sync_near_far", True):
         import torch.distributed as dist
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
             nearfar = global_near_far(scene.pose)
@@ -226,6 +226,30 @@ def shard_samples(batch: int, rank: int, world: int):
     return start, start + base + (1 if rank < extra else 0)
 
 
+def balanced_shards(costs, world: int):
+    """Deal the batch's samples to ``world`` ranks so that the ranks' summed ``costs`` are even: longest-processing-time
+    first under the constraint that no rank gets more than ceil(B / world) samples (every GPU holds its samples'
+    planes).  ``costs``: one positive number per sample, e.g. ``sample_cost_proxy``.  -> list of index lists.
+    A sample's render cost varies with how much of the image the body covers and how many part boxes overlap; contiguous
+    blocks (``shard_samples``) leave the slowest of 8 ranks ~15 % behind the mean on the benchmark batch."""
+    costs = [float(c) for c in costs]
+    cap = -(-len(costs) // world)
+    order = sorted(range(len(costs)), key=lambda i: -costs[i])
+    load, out = [0.0] * world, [[] for _ in range(world)]
+    for i in order:
+        r = min((r for r in range(world) if len(out[r]) < cap), key=lambda r: load[r])
+        out[r].append(i)
+        load[r] += costs[i]
+    return [sorted(b) for b in out]
+
+
+def sample_cost_proxy(pose_scaled, cscale=None):
+    """A cheap host-side estimate of a sample's render cost from its part frames alone (B,P,4,4): the number of
+    (point, part) pairs grows with the image area every part box covers, ~ sum over parts of 1 / depth^2."""
+    tz = pose_scaled[:, :, 2, 3].double().clamp_min(1e-3)
+    return (1.0 / tz ** 2).sum(dim=1).tolist()
+
+
 def global_near_far(pose_local, near0: float = NEAR_PLANE, far0: float = FAR_PLANE, group=None):
     """near/far over the WHOLE batch from this rank's shard of the (scaled) part frames (B_local,P,4,4).
 
@@ -269,19 +293,84 @@ def gather_rays(local: torch.Tensor, n_rays: int, group=None):
     return torch.cat(out, dim=-1)
 
 
+class _FromOwner(torch.autograd.Function):
+    """The owner rank's tensor on every rank (broadcast); in the backward the ranks' partial gradients are summed back
+    onto the owner (reduce), the other ranks get zeros.  Every rank passes a tensor of the same shape and dtype."""
+
+    @staticmethod
+    def forward(ctx, t, owner, group):
+        import torch.distributed as dist
+        ctx.owner, ctx.group = owner, group
+        out = t.detach().clone().contiguous()
+        dist.broadcast(out, src=owner, group=group)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        import torch.distributed as dist
+        g = g.contiguous().clone()
+        dist.reduce(g, dst=ctx.owner, op=dist.ReduceOp.SUM, group=ctx.group)
+        if dist.get_rank(ctx.group) != ctx.owner:
+            g.zero_()
+        return g, None, None
+
+
+class _GatherRays(torch.autograd.Function):
+    """``gather_rays`` with a gradient: every rank evaluates the same loss on the assembled tensor, so the gradient of
+    its own block is simply its slice of the incoming gradient (the sum over ranks happens where the blocks' shared
+    inputs are reduced, ``_FromOwner``)."""
+
+    @staticmethod
+    def forward(ctx, local, n_rays, group):
+        import torch.distributed as dist
+        ctx.range = shard_rays(n_rays, dist.get_rank(group), dist.get_world_size(group))
+        return gather_rays(local.detach(), n_rays, group)
+
+    @staticmethod
+    def backward(ctx, g):
+        lo, hi = ctx.range
+        return g[..., lo:hi].contiguous(), None, None
+
+
+def from_owner(t, owner=0, group=None):
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return t
+    return _FromOwner.apply(t, owner, group)
+
+
 def render_entire_img_sharded(model, pose_to_camera, inv_intrinsics, render_size: int = 128, Nc: int = 64, Nf: int = 128,
-                              model_input: Dict = {}, group=None, **kw):
-    """``render_entire_img`` with the image's rays split across the ranks of ``group`` (every rank holds the model and
-    the planes -- replicated parameters, or ``model_input["tri_plane_feature"]`` broadcast by the caller): rank r renders
-    rays ``shard_rays(n, r, world)``, one all_gather per output assembles the image on every rank.  No gradient path:
-    training shards samples, not rays (``shard_samples``)."""
+                              model_input: Dict = {}, group=None, no_grad: bool = True, owner: int = 0, **kw):
+    """``render_entire_img`` with the image's rays split across the ranks of ``group`` -- fewer samples than GPUs
+    (SURVEY 8e "B < G"; the reference renders the one image chunk by chunk on one GPU, rendering.py:362-427).
+    Rank r renders rays ``shard_rays(n, r, world)``; one all_gather per output assembles the image on every rank.
+
+    ``no_grad=True``: every rank holds the model and the planes (replicated parameters, or
+    ``model_input["tri_plane_feature"]`` given on every rank).
+    ``no_grad=False`` (training on one image): the OWNER's tri-plane and per-sample decoder weights are broadcast
+    (44 MB + 26 KB over NVLink), every rank renders and differentiates its ray block, and in the backward the partial
+    plane / decoder gradients are summed back onto the owner (one ``reduce`` each), where they flow on into whatever
+    produced them (tri-plane generator, modulation); the other ranks' parameters receive no gradient.  Every rank
+    must evaluate the same loss on the returned image."""
     import torch.distributed as dist
     world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
     rank = dist.get_rank(group) if world > 1 else 0
     bbox = kw.get("bbox")
     width, height = (bbox[2] - bbox[0], bbox[3] - bbox[1]) if bbox is not None else (render_size, render_size)
     n = width * height
+    mi = dict(model_input)
+    if not no_grad and world > 1:
+        with torch.set_grad_enabled(True):
+            tp = mi.get("tri_plane_feature")
+            if tp is None:
+                tp = model.compute_tri_plane_feature(mi["z"][:1], mi["bone_length"][:1], mi.get("truncation_psi", 1))
+            mi["tri_plane_feature"] = from_owner(tp[:1].to(torch.float32).contiguous(), owner, group)
+            mi["decoder"] = [(from_owner(w, owner, group), from_owner(b, owner, group))
+                             for w, b in model.mlp.effective(mi["z_rend"][:1])]
     color, mask, disp = render_entire_img(model, pose_to_camera, inv_intrinsics, render_size=render_size, Nc=Nc, Nf=Nf,
-                                          model_input=model_input, ray_range=shard_rays(n, rank, world), **kw)
-    color, mask, disp = gather_rays(color, n, group), gather_rays(mask, n, group), gather_rays(disp, n, group)
+                                          model_input=mi, ray_range=shard_rays(n, rank, world), no_grad=no_grad, **kw)
+    if world > 1 and not no_grad:
+        color, mask, disp = (_GatherRays.apply(t, n, group) for t in (color, mask, disp))
+    else:
+        color, mask, disp = gather_rays(color, n, group), gather_rays(mask, n, group), gather_rays(disp, n, group)
     return color.reshape(3, height, width), mask.reshape(height, width), disp.reshape(height, width)

@@ -44,6 +44,9 @@ def wrap_ddp(module: nn.Module, device: Optional[torch.device] = None, **kw) -> 
     if not any(p.requires_grad for p in module.parameters()):
         return module
     ids = [device.index] if device is not None and device.type == "cuda" else None
+    # buffers (canonical pose ...) are constants set identically on every rank: no per-forward broadcast
+    kw.setdefault("broadcast_buffers", False)
+    kw.setdefault("gradient_as_bucket_view", True)
     return nn.parallel.DistributedDataParallel(module, device_ids=ids, **kw)
 
 

@@ -7,7 +7,7 @@ import bench
 from enarf_gan_b200 import ops
 
 dev = torch.device("cuda", 0)
-w = bench.build_workload(0, 8, dev)
+w = bench.build_workload(list(range(8)), dev)
 w["tri_plane"][:, 96:] += 6.0
 w["decoder"][2] = (w["decoder"][2][0], w["decoder"][2][1] + torch.tensor([0, 0, 0, 30.0], device=dev))
 scene = ops.SceneBuffers(w["pose"], w["cscale"], w["canon"], w["tri_plane"], w["decoder"])

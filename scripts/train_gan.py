@@ -112,8 +112,8 @@ def main():
     gen, dis = build(device)
     gen_ddp, dis_ddp = train.wrap_ddp(gen, device), train.wrap_ddp(dis, device)
     cfg = train.StepConfig(z_total=256 * 3, n_accum_step=a.n_accum, adv_loss_type="ce", tri_plane_reg_coef=0.0)
-    go = torch.optim.Adam(gen_ddp.parameters(), lr=1e-3 * a.global_batch / 32, betas=(0.0, 0.99))
-    do = torch.optim.Adam(dis_ddp.parameters(), lr=2e-3 * a.global_batch / 32, betas=(0.0, 0.99))
+    go = torch.optim.Adam(gen_ddp.parameters(), lr=1e-4, betas=(0.0, 0.99))
+    do = torch.optim.Adam(dis_ddp.parameters(), lr=2e-4, betas=(0.0, 0.99))
     d = synthetic_batch(lo, B, device)
 
     def step(it, g_=gen_ddp, d_=dis_ddp):

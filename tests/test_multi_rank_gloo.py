@@ -83,3 +83,45 @@ def test_ray_sharding_gathers_the_whole_image(tmp_path):
         got = torch.load(os.path.join(tmp_path, f"g{r}.pt"))
         assert torch.equal(got["full"], torch.stack([ray, ray * 2, ray * 3]))
         assert torch.equal(got["mask"], ray + 0.5)
+
+
+# ---- B < G with gradients: the autograd collectives of rendering.render_entire_img_sharded ------------------------
+def _toy_render(planes, weight, lo, hi):
+    """A differentiable stand-in for a ray block's render: rays lo..hi read the shared planes / weights."""
+    rays = torch.arange(lo, hi, dtype=torch.float32)
+    return torch.sin(rays[None] * planes.sum() * 0.01) * weight.sum() + planes[0, lo:hi] * weight[0]
+
+
+def _grad_worker(rank, world, port, n, out_dir):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from enarf_gan_b200 import rendering
+        torch.manual_seed(3)
+        planes = torch.randn(1, n).requires_grad_()                # the owner's values count; others pass same-shaped junk
+        weight = torch.randn(2).requires_grad_()
+        if rank != 0:
+            planes = torch.zeros(1, n).requires_grad_()
+            weight = torch.zeros(2).requires_grad_()
+        p, w = rendering.from_owner(planes, 0), rendering.from_owner(weight, 0)
+        lo, hi = rendering.shard_rays(n, rank, world)
+        img = rendering._GatherRays.apply(_toy_render(p, w, lo, hi), n, None)
+        (img * torch.arange(n, dtype=torch.float32)).sum().backward()      # the same loss on every rank
+        torch.save({"img": img.detach(), "d_planes": planes.grad, "d_weight": weight.grad}, os.path.join(out_dir, f"g{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ray_sharded_gradients_sum_onto_the_owner(tmp_path):
+    n = 37                                           # uneven blocks
+    mp.spawn(_grad_worker, args=(2, _free_port(), n, str(tmp_path)), nprocs=2, join=True)
+    r0, r1 = (torch.load(os.path.join(tmp_path, f"g{r}.pt")) for r in range(2))
+    torch.manual_seed(3)
+    planes = torch.randn(1, n).requires_grad_()
+    weight = torch.randn(2).requires_grad_()
+    img = _toy_render(planes, weight, 0, n)
+    (img * torch.arange(n, dtype=torch.float32)).sum().backward()
+    assert torch.allclose(r0["img"], img.detach(), atol=1e-6) and torch.allclose(r1["img"], img.detach(), atol=1e-6)
+    assert torch.allclose(r0["d_planes"], planes.grad, rtol=1e-5, atol=1e-5), "owner: sum of both blocks' plane gradients"
+    assert torch.allclose(r0["d_weight"], weight.grad, rtol=1e-5, atol=1e-4)
+    assert r1["d_planes"].abs().sum() == 0 and r1["d_weight"].abs().sum() == 0, "non-owners receive no gradient"
