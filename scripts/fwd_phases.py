@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, bench
 from enarf_gan_b200 import _abi
 dev = torch.device("cuda:0"); torch.cuda.set_device(0)
-w = bench.build_workload(0, 8, dev)
+w = bench.build_workload(list(range(8)), dev)
 for i in range(2): bench.step_device(w, i)
 torch.cuda.synchronize()
 lib = _abi.lib()

@@ -6,7 +6,7 @@ import torch
 import bench
 dev = torch.device("cuda:0")
 torch.cuda.set_device(0)
-w = bench.build_workload(0, 8, dev)
+w = bench.build_workload(list(range(8)), dev)
 gen, host, out_img, out_loss, h2d, d2h = bench.build_e2e(w, dev)
 for _ in range(3):
     bench.step_e2e(gen, host, out_img, out_loss, dev)
