@@ -39,6 +39,7 @@ def parse_args():
     ap.add_argument("--global-batch", type=int, default=GLOBAL_BATCH)
     ap.add_argument("--shard", default="balanced", choices=["balanced", "contiguous"],
                     help="how the global batch is dealt to the ranks (strong scaling)")
+    ap.add_argument("--eager-e2e", action="store_true", help="end-to-end arm without the CUDA graph (GraphedRenderStep)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true", help="skip timing the reference's eager path on this GPU")
     return ap.parse_args()
@@ -195,7 +196,7 @@ def step_device(w, step_idx, timer=None, world=None):
             scene.ref, p(dmin), p(dmax), p(direction), p(bins), p(pts), p(feat), pairs.ref, n, NF, p(w["g_color"]), p(w["g_mask"]),
             None, None,
             p(d_feat), d_tp[:, 96:].data_ptr(), d_tp.stride(0), p(dw[0]), p(dw[1]), p(dw[2]), p(db[0]), p(db[1]), p(db[2]),
-            0.0, ops.stream_ptr()))
+            0.0, 0.0, ops.stream_ptr()))
     timed("fine_bwd", bwd)
     timed("unpack", lambda: ops.unpack_plane_grads(d_feat, d_tp, accumulate=False))
     w["last"] = (color, mask, d_tp, dw, bins, dmin, dmax, direction)
@@ -236,7 +237,7 @@ class _Planes(torch.nn.Module):
         return self.tp if z.shape[0] == self.tp.shape[0] else self.tp[:z.shape[0]]
 
 
-def build_e2e(w, device):
+def build_e2e(w, device, graph=True):
     from enarf_gan_b200 import synthetic as S
     from enarf_gan_b200.generator import TriNARFGenerator
     cfg = dict(z_dim=256, background_ratio=0.7,
@@ -255,16 +256,29 @@ def build_e2e(w, device):
     out_loss = torch.empty(1).pin_memory()
     h2d = sum(t.numel() * t.element_size() for t in host.values())
     d2h = out_img.numel() * 4 + 4
+    if graph and w["B"] >= 2:
+        # the public graphed step (enarf_gan_b200.graphed): generator forward + loss + backward captured once
+        from enarf_gan_b200.graphed import GraphedRenderStep
+        order = ("pose_to_camera", "pose_to_world", "bone_length", "z", "inv_intrinsics")
+        gen = GraphedRenderStep(gen, e2e_loss, *[host[k] for k in order], device=device)
     return gen, host, out_img, out_loss, h2d, d2h
 
 
+def e2e_loss(color, mask):
+    return (color ** 2).mean() + ((1 - mask) ** 2).mean()
+
+
 def step_e2e(gen, host, out_img, out_loss, device):
-    dev = {k: v.to(device, non_blocking=True) for k, v in host.items()}
-    gen.zero_grad(set_to_none=True)
-    color, mask, fw, fd = gen(dev["pose_to_camera"], dev["pose_to_world"], dev["bone_length"], dev["z"],
-                              dev["inv_intrinsics"])
-    loss = (color ** 2).mean() + ((1 - mask) ** 2).mean()
-    loss.backward()
+    if not isinstance(gen, torch.nn.Module):         # graphed: pinned host tensors in, static device tensors out
+        color, mask, loss = gen(host["pose_to_camera"], host["pose_to_world"], host["bone_length"], host["z"],
+                                host["inv_intrinsics"])
+    else:
+        dev = {k: v.to(device, non_blocking=True) for k, v in host.items()}
+        gen.zero_grad(set_to_none=True)
+        color, mask, fw, fd = gen(dev["pose_to_camera"], dev["pose_to_world"], dev["bone_length"], dev["z"],
+                                  dev["inv_intrinsics"])
+        loss = e2e_loss(color, mask)
+        loss.backward()
     out_img.copy_(color.detach(), non_blocking=True)
     out_loss.copy_(loss.detach().reshape(1), non_blocking=True)
 
@@ -511,7 +525,7 @@ def main():
     kt = timer.totals()
     overflow = int((w["ckpt_tile_base"] < 0).sum().item())     # tiles of the last step whose pairs did not fit the checkpoint
     # ---- end-to-end arm (host buffers in, image + loss out) ----
-    gen, host, out_img, out_loss, h2d, d2h = build_e2e(w, device)
+    gen, host, out_img, out_loss, h2d, d2h = build_e2e(w, device, graph=not args.eager_e2e)
     for _ in range(max(3, args.warmup)):
         step_e2e(gen, host, out_img, out_loss, device)
     sync()
@@ -542,7 +556,9 @@ def main():
     line["gpu_launches"] = launches
     line["points_per_s"] = value * (NC + NF)
     line["e2e"] = {"value": rays / (ms_e2e * 1e-3), "unit": "rays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                   "ms_per_step": ms_e2e, "api": "TriNARFGenerator.forward + loss.backward (pinned host inputs)"}
+                   "ms_per_step": ms_e2e, "api": ("TriNARFGenerator.forward + loss.backward (pinned host inputs)" if args.eager_e2e or B < 2 else
+                           "graphed.GraphedRenderStep(TriNARFGenerator, loss): forward + loss + backward replayed from one CUDA "
+                           "graph (pinned host inputs copied in, image + loss copied out)")}
     if per_rank is not None:
         # [device ms, e2e ms, sum of kernel ms] of every rank: the spread is the load imbalance (each rank's samples have
         # their own mean valid parts per point); there is no collective on the path

@@ -42,12 +42,12 @@ _SIGNATURES = {
     "enarf_near_far": (c_int, [_P, c_int, c_int, c_float, c_float, _P, _P]),
     "enarf_depth_range": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
     "enarf_render_coarse": (c_int, [POINTER(Scene), _P, _P, _P, c_int, c_int, _P, _P, _P, c_float, _P, _P, _P]),
-    "enarf_fine_sample": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, c_uint64, c_int64, _P, _P, _P]),
+    "enarf_fine_sample": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, c_uint64, _P, c_int64, _P, _P, _P]),
     "enarf_fine_tiles_per_sample": (c_int, [c_int, c_int]),
     "enarf_render_fine_fwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, c_int, c_int, _P, _P, _P, _P, _P, _P, _P,
-                                      POINTER(PairCkpt), c_float, _P, _P, _P]),
+                                      POINTER(PairCkpt), c_float, _P, _P, c_float, _P]),
     "enarf_render_fine_bwd": (c_int, [POINTER(Scene), _P, _P, _P, _P, _P, _P, POINTER(PairCkpt), c_int, c_int, _P, _P, _P, _P,
-                                      _P, _P, c_int64, _P, _P, _P, _P, _P, _P, c_float, _P]),
+                                      _P, _P, c_int64, _P, _P, _P, _P, _P, _P, c_float, c_float, _P]),
     "enarf_density_query": (c_int, [POINTER(Scene), _P, c_int, _P, _P, _P, _P]),
     "enarf_triplane_sample_fwd": (c_int, [_P, _P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                           _P, _P]),

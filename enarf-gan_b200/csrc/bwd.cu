@@ -48,6 +48,7 @@ struct BwdArgs {
     float *d_w1, *d_w2, *d_w3, *d_b1, *d_b2, *d_b3;
     int rays_per_tile, tiles_per_sample;
     int* tile_counter;
+    float bg_const;           // the forward composited colour = rgb + (1 - mask) * bg_const
     float ert_eps;            // > 0: the forward ran with early ray termination (group-major pair order, dropped samples)
 };
 
@@ -341,7 +342,8 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             s.rg[tid * 8 + 0] = gc ? gc[0] : 0.f;
             s.rg[tid * 8 + 1] = gc ? gc[n] : 0.f;
             s.rg[tid * 8 + 2] = gc ? gc[2 * (size_t)n] : 0.f;
-            s.rg[tid * 8 + 3] = a.g_mask ? a.g_mask[o] : 0.f;
+            // d mask also collects the composite's share: d/d mask of (1 - mask) * bg summed over the three channels
+            s.rg[tid * 8 + 3] = (a.g_mask ? a.g_mask[o] : 0.f) - a.bg_const * (s.rg[tid * 8] + s.rg[tid * 8 + 1] + s.rg[tid * 8 + 2]);
             s.rg[tid * 8 + 4] = a.g_disp ? a.g_disp[o] : 0.f;
         }
         {
@@ -611,7 +613,7 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
                                      const float* g_color, const float* g_mask, const float* g_disparity,
                                      const float* g_fine_weights, float* d_feat, float* d_prob,
                                      int64_t d_prob_batch_stride, float* d_w1, float* d_w2, float* d_w3, float* d_b1,
-                                     float* d_b2, float* d_b3, float ert_eps, void* stream) {
+                                     float* d_b2, float* d_b3, float ert_eps, float bg_const, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_bwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && point_saved, ENARF_ERR_INVALID_ARG,
@@ -653,6 +655,7 @@ extern "C" int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* de
     a.d_b2 = d_b2;
     a.d_b3 = d_b3;
     a.ert_eps = ert_eps;
+    a.bg_const = bg_const;
     a.rays_per_tile = max(1, min(MAX_RAYS, TP_MAX / Nf));
     a.tiles_per_sample = (n + a.rays_per_tile - 1) / a.rays_per_tile;
     const int total = scene->B * a.tiles_per_sample;

@@ -61,6 +61,7 @@ struct RenderArgs {
     int ert_min_count;
     int* ert_stats;         // [0] += active points evaluated, [1] += active points skipped
     int* opaque_rays;       // coarse pass: += rays whose coarse transmittance ends below OPAQUE_T
+    float bg_const;         // fine pass: colour out = rgb + (1 - mask) * bg_const (models/generator.py:105-107; 0 = foreground)
 };
 #define OPAQUE_T 1e-2f
 
@@ -310,9 +311,10 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 }
                 if (lane == 0) {
                     float* c = a.color + (size_t)b * 3 * n + ray0 + r;
-                    c[0] = cr;
-                    c[n] = cg;
-                    c[2 * (size_t)n] = cb;
+                    const float bgc = (1.f - cm) * a.bg_const;   // constant background composited in the epilogue
+                    c[0] = cr + bgc;
+                    c[n] = cg + bgc;
+                    c[2 * (size_t)n] = cb + bgc;
                     a.mask[gray] = cm;
                     a.disp[gray] = cd;
                 }
@@ -405,7 +407,7 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
                                      const float* ray_dir, const float* bins, int n, int Nf, float* color,
                                      float* mask, float* disparity, float* fine_weights, float* fine_depth,
                                      float* point_out, float* feat_out, const enarf_pair_ckpt_t* pair_ckpt, float ert_eps,
-                                     const int* ert_hint, int* ert_stats, void* stream) {
+                                     const int* ert_hint, int* ert_stats, float bg_const, void* stream) {
     int rc = enarf_check_scene(scene, "enarf_render_fine_fwd");
     if (rc) return rc;
     ENARF_REQUIRE(depth_min && depth_max && ray_dir && bins && color && mask && disparity && fine_weights && fine_depth,
@@ -438,6 +440,7 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
     a.ert_hint = ert_hint;
     a.ert_min_count = max(1, (int)(((long long)scene->B * n) / 64));   // rounds pay once ~1.5 % of the rays are opaque
     a.ert_stats = ert_stats;
+    a.bg_const = bg_const;
     if (pair_ckpt) {
         ENARF_REQUIRE(pair_ckpt->rec && pair_ckpt->feat && pair_ckpt->tile_base && pair_ckpt->cursor && pair_ckpt->capacity > 0 &&
                           ((uintptr_t)pair_ckpt->rec & 15) == 0 && ((uintptr_t)pair_ckpt->feat & 15) == 0,

@@ -9,9 +9,10 @@
 
 __global__ void __launch_bounds__(WARPS * 32) fine_sample_kernel(
     const float* __restrict__ weights, int R, int Nc, int Nf, int Nf2, int mode, const int32_t* __restrict__ idx_in,
-    const float* __restrict__ jitter, uint64_t seed, int64_t ray_id_offset, float* __restrict__ bins_out,
-    int32_t* __restrict__ idx_out) {
+    const float* __restrict__ jitter, uint64_t seed, const uint64_t* __restrict__ seed_dev, int64_t ray_id_offset,
+    float* __restrict__ bins_out, int32_t* __restrict__ idx_out) {
     extern __shared__ float smem[];
+    if (seed_dev) seed += *seed_dev;   // a seed that lives on the device: a captured CUDA graph draws afresh on every replay
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     float* cdf = smem + warp * (Nc + Nf2);
     float* val = cdf + Nc;
@@ -116,8 +117,8 @@ __global__ void __launch_bounds__(WARPS * 32) fine_sample_kernel(
 }
 
 extern "C" int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, const int32_t* idx,
-                                 const float* jitter, uint64_t seed, int64_t ray_id_offset, float* bins_out,
-                                 int32_t* idx_out, void* stream) {
+                                 const float* jitter, uint64_t seed, const uint64_t* seed_dev, int64_t ray_id_offset,
+                                 float* bins_out, int32_t* idx_out, void* stream) {
     ENARF_REQUIRE(bins_out && R > 0 && Nc >= 2 && Nf >= 1, ENARF_ERR_INVALID_ARG, "enarf_fine_sample: bad arguments");
     ENARF_REQUIRE(Nc <= 1024 && Nf <= 1024, ENARF_ERR_UNSUPPORTED, "enarf_fine_sample: Nc=%d Nf=%d too large", Nc, Nf);
     if (mode == ENARF_RNG_GIVEN) {
@@ -132,7 +133,7 @@ extern "C" int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, in
     const size_t smem = (size_t)WARPS * (Nc + Nf2) * sizeof(float);
     const int grid = min((R + WARPS - 1) / WARPS, 16 * enarf_sm_count());
     fine_sample_kernel<<<grid, WARPS * 32, smem, (cudaStream_t)stream>>>(weights, R, Nc, Nf, Nf2, mode, idx, jitter, seed,
-                                                                         ray_id_offset, bins_out, idx_out);
+                                                                         seed_dev, ray_id_offset, bins_out, idx_out);
     ENARF_CHECK_LAUNCH("enarf_fine_sample");
     return ENARF_OK;
 }

@@ -73,9 +73,13 @@ class TriNARFGenerator(nn.Module):
             inv_intrinsics = torch.from_numpy(inv_intrinsics)
         inv_intrinsics = inv_intrinsics.float().to(device)
         nparams = _cfg(self.config, "nerf_params")
+        # a constant (black) background is composited inside the fine pass's epilogue; an image background, or a caller
+        # who wants the bare foreground back (return_bg), goes through the torch expression below
+        const_bg = (self.black_background or black_bg_if_possible) and not return_bg
         out = self.nerf(batchsize, homo_img, pose_to_camera, inv_intrinsics, z_nerf, z_rend, bone_length,
                         Nc=_cfg(nparams, "Nc"), Nf=_cfg(nparams, "Nf"), return_intermediate=return_intermediate,
-                        truncation_psi=truncation_psi, return_disparity=return_disparity)
+                        truncation_psi=truncation_psi, return_disparity=return_disparity,
+                        background=-1.0 if const_bg else 0.0)
         fg_color, fg_mask = out[:2]
         fine_weights = self.nerf.buffers_tensors.get("fine_weights")
         fine_depth = self.nerf.buffers_tensors.get("fine_depth")
@@ -86,7 +90,7 @@ class TriNARFGenerator(nn.Module):
             bg_color, _ = self.background_generator([z_bg, z_rend], inject_index=n_latent - 4)
         else:
             bg_color = -1
-        rendered_color = fg_color + (1 - fg_mask[:, None]) * bg_color
+        rendered_color = fg_color if const_bg else fg_color + (1 - fg_mask[:, None]) * bg_color      # generator.py:107
         if return_intermediate:
             fine_points, fine_density = out[-1]
             return rendered_color, fg_mask, fine_points, fine_density
@@ -178,12 +182,12 @@ class DSONARFGenerator(nn.Module):
         grid, img_coord = self.ray_sampler(mask, _cfg(self.config, "ray_batchsize"))
         z1, z2 = self.get_latents(frame_time, pose_to_camera)
         nparams = _cfg(self.config, "nerf_params")
-        color, rendered_mask = self.nerf(batchsize, img_coord, pose_to_camera, inv_intrinsics, z1, z2, bone_length,
-                                         Nc=_cfg(nparams, "Nc"), Nf=_cfg(nparams, "Nf"), return_intermediate=False,
-                                         camera_pose=camera_pose)
         if background is None:
             background = -1
-        color = color + background * (1 - rendered_mask[:, None])
+        # composited in the fine pass's epilogue: color + background * (1 - mask), models/generator.py:255-257
+        color, rendered_mask = self.nerf(batchsize, img_coord, pose_to_camera, inv_intrinsics, z1, z2, bone_length,
+                                         Nc=_cfg(nparams, "Nc"), Nf=_cfg(nparams, "Nf"), return_intermediate=False,
+                                         camera_pose=camera_pose, background=float(background))
         return color, rendered_mask, grid
 
     def render_entire_img(self, pose_to_camera, inv_intrinsics, frame_time, bone_length, camera_pose=None,

@@ -245,12 +245,18 @@ class TriPlaneNARF(nn.Module):
     # ---- NARFBase.forward / render_entire_img (libraries/NARF/base.py:26-63) --------------------------
     def forward(self, batchsize, sampled_img_coord, pose_to_camera, inv_intrinsics, z, z_rend, bone_length,
                 render_scale=1, Nc=64, Nf=128, return_intermediate=False, truncation_psi=1,
-                camera_pose: Optional[torch.Tensor] = None, return_disparity=False):
+                camera_pose: Optional[torch.Tensor] = None, return_disparity=False, background: float = 0.0):
+        """``background``: a constant the colour is composited over inside the fine pass (rgb + (1 - mask) * background)
+        instead of three element-wise passes in the caller; 0 = the reference's plain foreground colour."""
         model_input = {"z": z, "z_rend": z_rend, "bone_length": bone_length, "truncation_psi": truncation_psi}
         pose_to_camera, model_input["bone_length"] = self.transform_pose(pose_to_camera, bone_length)
-        out = rendering.render(self, sampled_img_coord, pose_to_camera, inv_intrinsics, render_scale=render_scale,
-                               Nc=Nc, Nf=Nf, return_intermediate=return_intermediate, camera_pose=camera_pose,
-                               model_input=model_input)
+        self._bg_const = float(background)
+        try:
+            out = rendering.render(self, sampled_img_coord, pose_to_camera, inv_intrinsics, render_scale=render_scale,
+                                   Nc=Nc, Nf=Nf, return_intermediate=return_intermediate, camera_pose=camera_pose,
+                                   model_input=model_input)
+        finally:
+            self._bg_const = 0.0
         if return_intermediate:
             color, mask, _, inter = out
             return color, mask, inter

@@ -187,8 +187,9 @@ def render_coarse(scene, dmin, dmax, direction, Nc, want_density=False, opaque_r
     return (wb, den) if want_density else wb
 
 
-def fine_sample(weights, Nf, idx=None, jitter=None, seed=0, ray_id_offset=0, want_idx=False):
-    """weights (...,Nc) -> sorted bins (...,Nf).  idx+jitter given -> parity mode, else Philox."""
+def fine_sample(weights, Nf, idx=None, jitter=None, seed=0, ray_id_offset=0, want_idx=False, seed_dev=None):
+    """weights (...,Nc) -> sorted bins (...,Nf).  idx+jitter given -> parity mode, else Philox with key
+    ``seed`` (+ ``seed_dev``: a one-element int64 device tensor, for renders replayed from a CUDA graph)."""
     Nc = weights.shape[-1]
     R = weights.numel() // Nc
     bins = torch.empty(*weights.shape[:-1], Nf, device=weights.device)
@@ -200,7 +201,8 @@ def fine_sample(weights, Nf, idx=None, jitter=None, seed=0, ray_id_offset=0, wan
     else:
         mode = _abi.RNG_PHILOX
     check(lib().enarf_fine_sample(ptr(weights), R, Nc, Nf, mode, ptr(idx, torch.int32, True), ptr(jitter, allow_none=True),
-                                  seed, ray_id_offset, ptr(bins), ptr(idx_out, torch.int32, True), stream_ptr()))
+                                  seed, ptr(seed_dev, torch.int64, True), ray_id_offset, ptr(bins),
+                                  ptr(idx_out, torch.int32, True), stream_ptr()))
     return (bins, idx_out) if want_idx else bins
 
 
@@ -250,7 +252,7 @@ class PairCheckpoint:
 
 
 def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False, want_pairs=False,
-                     ert_eps=0.0, ert_hint=None, ert_stats=None):
+                     ert_eps=0.0, ert_hint=None, ert_stats=None, bg_const=0.0):
     """-> color, mask, disp, fine_weights, fine_depth [, points (B,n,Nf,4)] [, feat (B,n,Nf,32) checkpoint: only
     the rows of samples inside a part are written] [, PairCheckpoint]."""
     B, n, Nf = bins.shape
@@ -266,7 +268,8 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
                                       ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True),
                                       ptr(feat, allow_none=True), pairs.ref if pairs else None, float(ert_eps),
-                                      ptr(ert_hint, torch.int32, True), ptr(ert_stats, torch.int32, True), stream_ptr()))
+                                      ptr(ert_hint, torch.int32, True), ptr(ert_stats, torch.int32, True), float(bg_const),
+                                      stream_ptr()))
     out = (color, mask, disp, fw, fd)
     if want_points:
         out += (pts,)
@@ -279,12 +282,14 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
 
 def _fine_forward(ctx, scene, dmin, dmax, direction, bins, ert):
     """Forward of both autograd Functions: run the fused pass with the checkpoints a backward wants and stash them.
-    ``ert`` = (ert_eps, ert_hint, ert_stats) of the early ray termination."""
+    ``ert`` = (ert_eps, ert_hint, ert_stats[, bg_const]): early ray termination and the constant background."""
     pairs_on = SAVE_FEATURES and PAIR_CKPT
     out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
-                           want_pairs=pairs_on, ert_eps=ert[0], ert_hint=ert[1], ert_stats=ert[2])
+                           want_pairs=pairs_on, ert_eps=ert[0], ert_hint=ert[1], ert_stats=ert[2],
+                           bg_const=ert[3] if len(ert) > 3 else 0.0)
     ctx.scene = scene
     ctx.ert_eps = float(ert[0])
+    ctx.bg_const = float(ert[3]) if len(ert) > 3 else 0.0
     saved = [dmin, dmax, direction, bins, out[5]]
     if SAVE_FEATURES:
         saved.append(out[6])
@@ -313,7 +318,8 @@ def _fine_backward(ctx, grads, d_feat, d_prob, d_prob_stride):
         pairs.ref if pairs else None, n, Nf,
         ptr(g[0], allow_none=True), ptr(g[1], allow_none=True), ptr(g[2], allow_none=True),
         ptr(g[3], allow_none=True), ptr(d_feat), d_prob.data_ptr(), d_prob_stride,
-        ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), ctx.ert_eps, stream_ptr()))
+        ptr(dw[0]), ptr(dw[1]), ptr(dw[2]), ptr(db[0]), ptr(db[1]), ptr(db[2]), ctx.ert_eps, ctx.bg_const,
+        stream_ptr()))
     return (dw[0], dw[1], dw[2], db[0].reshape(ctx_shape(scene, 0)), db[1].reshape(ctx_shape(scene, 1)),
             db[2].reshape(ctx_shape(scene, 2)))
 
@@ -383,13 +389,14 @@ def ctx_shape(scene, i):
 
 
 def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None, want_points=None, ert_eps=0.0,
-                ert_hint=None, ert_stats=None):
+                ert_hint=None, ert_stats=None, bg_const=0.0):
     """-> color (B,3,n), mask (B,n), disparity (B,n), fine_weights (B,n,Nf-1), fine_depth (B,n,Nf)
     [, points (B,n,Nf,4) = per-sample (r,g,b,sigma) when ``want_points`` is given (None/False/True)].
-    Pass the autograd-tracked ``tri_plane`` and ``decoder`` tensors to get gradients."""
+    Pass the autograd-tracked ``tri_plane`` and ``decoder`` tensors to get gradients.  ``bg_const``: colour comes out
+    composited over a constant background, rgb + (1 - mask) * bg_const."""
     if tri_plane is None or not torch.is_grad_enabled():
         out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=bool(want_points), ert_eps=ert_eps,
-                               ert_hint=ert_hint, ert_stats=ert_stats)
+                               ert_hint=ert_hint, ert_stats=ert_stats, bg_const=bg_const)
         if ert_eps > 0 and not want_points:
             out = out[:5]                       # the point records were only needed to mark the dropped samples
         return out if want_points is None or want_points else out + (None,)
@@ -397,8 +404,8 @@ def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
     if isinstance(tri_plane, (tuple, list)):        # (feat_planes channels-last, prob_planes NCHW)
         out = RenderFinePlanes.apply(scene, dmin, dmax, direction, bins, tri_plane[0], tri_plane[1], w1, w2, w3, b1, b2, b3,
-                                     (ert_eps, ert_hint, ert_stats))
+                                     (ert_eps, ert_hint, ert_stats, bg_const))
         return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
     out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3,
-                           (ert_eps, ert_hint, ert_stats))
+                           (ert_eps, ert_hint, ert_stats, bg_const))
     return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))

@@ -26,9 +26,10 @@ def pixel_grid(render_size, patch_size, batchsize, device):
 
 
 @on_device_of(1)
-def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rng="philox", seed=0,
+def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rng="philox", seed=0, seed_dev=None,
                 idx=None, jitter=None, compact_b1=True, tri_plane=None, decoder=None, nearfar=None,
-                generator=None, return_intermediate=False, want_points=False, ert_eps=0.0, ert_prev=None):
+                generator=None, return_intermediate=False, want_points=False, ert_eps=0.0, ert_prev=None,
+                bg_const=0.0):
     """image_coord (B,3,n) homogeneous pixels -> dict(color (B,3,n), mask (B,n), disparity (B,n),
     fine_weights (B,n',Nf-1), fine_depth (B,n',Nf), validity (B,n)); n' = valid rays when B == 1
     (rendering.py:107-110), else n.
@@ -38,6 +39,9 @@ def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rn
     Rounds (extra barriers) only run where rays are opaque: the fine pass asks this call's coarse pass, the coarse pass
     asks ``ert_prev`` = out["opaque_rays"] of the previous call on this scene (None: assume translucent).
     out["ert_stats"] is an int32 (4,) on the device: fine samples evaluated, skipped, coarse evaluated, skipped.
+
+    bg_const: colour = rgb + (1 - mask) * bg_const, composited in the fine pass's epilogue (rays that are not rendered
+    come out as bg_const).
 
     rng: "philox" (in-kernel draws, counter = launch ray index), "torch" (torch.multinomial + uniform_ on
     the device generator, the reference's own order, rendering.py:192-194) or "given" (idx, jitter).
@@ -58,7 +62,7 @@ def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rn
         direction = direction[:, :, sel].contiguous()
     n = dmin.shape[1]
     if n == 0:                                      # rendering.py:351-354
-        out.update(color=torch.zeros(B, 3, n_all, device=dev), mask=torch.zeros(B, n_all, device=dev),
+        out.update(color=torch.full((B, 3, n_all), float(bg_const), device=dev), mask=torch.zeros(B, n_all, device=dev),
                    disparity=torch.zeros(B, n_all, device=dev), fine_weights=None, fine_depth=None)
         return out
     hint = stats = None
@@ -70,7 +74,7 @@ def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rn
         wb = ops.render_coarse(scene, dmin, dmax, direction, Nc, opaque_rays=hint, ert_eps=ert_eps,
                                ert_hint=prev if ert_eps > 0 else None, ert_stats=stats[2:] if ert_eps > 0 else None)
         if rng == "philox":
-            bins = ops.fine_sample(wb, Nf, seed=seed)
+            bins = ops.fine_sample(wb, Nf, seed=seed, seed_dev=seed_dev)
         elif rng == "torch":
             idx = torch.multinomial(wb.reshape(B * n, Nc), Nf, replacement=True, generator=generator)
             jitter = torch.empty(B, 1, n, Nf, device=dev).uniform_(generator=generator)
@@ -80,14 +84,14 @@ def render_rays(scene: ops.SceneBuffers, image_coord, inv_intrinsics, Nc, Nf, rn
         else:
             raise ValueError(f"unknown rng mode {rng!r}")
     color, mask, disp, fw, fd, pts = ops.render_fine(scene, dmin, dmax, direction, bins, tri_plane, decoder,
-                                                     want_points=want_points, ert_eps=ert_eps, ert_hint=hint,
+                                                     want_points=want_points, bg_const=bg_const, ert_eps=ert_eps, ert_hint=hint,
                                                      ert_stats=stats[:2] if ert_eps > 0 else None)
     if ert_eps > 0:
         out["ert_stats"] = stats
         if pts is not None:
             pts = torch.cat([pts[..., :3], pts[..., 3:].clamp_min(0)], dim=-1)    # dropped samples are marked sigma = -1
     if sel is not None:                             # rendering.py:337-350
-        full_c = torch.zeros(B, 3, n_all, device=dev).index_copy(2, sel, color)
+        full_c = torch.full((B, 3, n_all), float(bg_const), device=dev).index_copy(2, sel, color)
         full_m = torch.zeros(B, n_all, device=dev).index_copy(1, sel, mask)
         full_d = torch.zeros(B, n_all, device=dev).index_copy(1, sel, disp)
         color, mask, disp = full_c, full_m, full_d
@@ -140,16 +144,21 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
             nearfar = global_near_far(scene.pose)
     out = render_rays(scene, image_coord.reshape(B, 3, n_all), inv_intrinsics, Nc, Nf, nearfar=nearfar,
                       rng=getattr(model, "rng_mode", "torch"), seed=getattr(model, "rng_seed", 0),
+                      seed_dev=getattr(model, "rng_seed_dev", None),
                       idx=getattr(model, "rng_given", (None, None))[0],
                       jitter=getattr(model, "rng_given", (None, None))[1],
                       tri_plane=tri_plane if track else None, decoder=decoder if track else None,
                       return_intermediate=return_intermediate or not model.training, want_points=True,
-                      ert_eps=float(getattr(model, "ert_eps", 0.0)), ert_prev=getattr(model, "_ert_prev", None))
+                      ert_eps=float(getattr(model, "ert_eps", 0.0)), ert_prev=getattr(model, "_ert_prev", None),
+                      bg_const=float(getattr(model, "_bg_const", 0.0)))
     if "ert_stats" in out:
         model.buffers_tensors["ert_stats"] = out["ert_stats"]
         model._ert_prev = out["opaque_rays"]        # the next call's coarse pass decides on it whether to run in rounds
     if getattr(model, "rng_mode", "torch") == "philox":
-        model.rng_seed = getattr(model, "rng_seed", 0) + 1      # fresh draws on the next call
+        if getattr(model, "rng_seed_dev", None) is not None:
+            model.rng_seed_dev.add_(1)                          # on the device: also advances inside a replayed CUDA graph
+        else:
+            model.rng_seed = getattr(model, "rng_seed", 0) + 1  # fresh draws on the next call
     if out["fine_weights"] is not None:
         n = out["fine_weights"].shape[1]
         model.buffers_tensors["fine_weights"] = out["fine_weights"][:, None]

@@ -117,10 +117,12 @@ int enarf_render_coarse(const enarf_scene_t* scene, const float* depth_min, cons
 
 /* Hierarchical sampling (rendering.py:192-197): per ray draw Nf bins from the blurred coarse weights,
  * bins = idx/Nc + jitter/Nc, sorted ascending.  weights (R,Nc).  mode GIVEN: idx (R,Nf) int32 and jitter
- * (R,Nf) are inputs.  mode PHILOX: counter = (ray_id_offset + ray, sample), key = seed; idx_out optional. */
+ * (R,Nf) are inputs.  mode PHILOX: counter = (ray_id_offset + ray, sample), key = seed + *seed_dev (seed_dev: one
+ * uint64 in device memory, optional -- a render captured in a CUDA graph keeps its seed there and bumps it with a
+ * captured add, so every replay draws afresh); idx_out optional. */
 int enarf_fine_sample(const float* weights, int R, int Nc, int Nf, int mode, const int32_t* idx,
-                      const float* jitter, uint64_t seed, int64_t ray_id_offset, float* bins_out,
-                      int32_t* idx_out, void* stream);
+                      const float* jitter, uint64_t seed, const uint64_t* seed_dev, int64_t ray_id_offset,
+                      float* bins_out, int32_t* idx_out, void* stream);
 
 /* Optional per-(sample point, part) checkpoint written by the fine forward and consumed by the fine backward, so
  * that the backward neither rebuilds its pair records (canonical coordinates, bilinear footprints, 12 probability
@@ -151,12 +153,14 @@ int enarf_fine_tiles_per_sample(int n, int Nf);
  * in point_out with sigma = -1, from which the backward (same ert_eps) leaves them out as well.  point_out is then
  * mandatory.  ert_hint (one int, optional): enarf_render_coarse's opaque_rays -- with fewer than B*n/64 opaque rays
  * everything is evaluated in one round (no extra barriers); NULL = always in rounds.  ert_stats (two ints, optional):
- * [0] += samples evaluated, [1] += samples skipped.  ert_eps = 0: off, the reference's exact semantics. */
+ * [0] += samples evaluated, [1] += samples skipped.  ert_eps = 0: off, the reference's exact semantics.
+ * bg_const: constant background composited in the epilogue, color = rgb + (1 - mask) * bg_const (the generator's
+ * fg + (1 - mask) * bg with its black background bg = -1, models/generator.py:101-107; 0 = plain foreground). */
 int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, int n, int Nf, float* color, float* mask,
                           float* disparity, float* fine_weights, float* fine_depth, float* point_out,
                           float* feat_out, const enarf_pair_ckpt_t* pair_ckpt /* NULL = none */, float ert_eps,
-                          const int* ert_hint, int* ert_stats, void* stream);
+                          const int* ert_hint, int* ert_stats, float bg_const, void* stream);
 
 /* Fine pass backward.  point_saved (B,n,Nf,4) is the forward's point_out; feat_saved (B,n,Nf,32) is the forward's
  * feat_out or NULL (the features are then gathered again); pair_ckpt requires feat_saved.  Upstream gradients (any may be NULL = zero):
@@ -164,13 +168,14 @@ int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* depth_min, co
  * zero-initialises; results are ADDED): d_feat (B,3,H,W,32) fp32 channels-last, d_prob same layout/stride as
  * scene->prob_planes, d_w1 (B,64,32), d_w2 (B,64,64), d_w3 (B,4,64), d_b1 (64), d_b2 (64), d_b3 (4).
  * ert_eps: the value the forward was called with (> 0: the samples it dropped, sigma < 0 in point_saved, take no part
- * and carry no gradient; the tile's pair order is the forward's). */
+ * and carry no gradient; the tile's pair order is the forward's); bg_const: the forward's (g_color then also feeds
+ * d mask through the composite). */
 int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, const float* depth_max,
                           const float* ray_dir, const float* bins, const float* point_saved, const float* feat_saved,
                           const enarf_pair_ckpt_t* pair_ckpt /* the forward's, or NULL */, int n, int Nf, const float* g_color, const float* g_mask, const float* g_disparity,
                           const float* g_fine_weights, float* d_feat, float* d_prob, int64_t d_prob_batch_stride,
                           float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, float ert_eps,
-                          void* stream);
+                          float bg_const, void* stream);
 
 /* Point query = calc_density_and_color_from_camera_coord_v2 (models/narf.py:176-211): points (B,3,N) in
  * the scaled camera frame -> density (B,1,N), color (B,3,N) (NULL to skip), part_mask (B,N) uint32 bit p =

@@ -36,7 +36,7 @@ def test_argument_errors_do_not_need_a_gpu(built):
     rc = lib.enarf_near_far(None, 1, 1, 0.3, 5.0, None, None)
     assert rc == 1
     assert b"enarf_near_far" in lib.enarf_last_error()
-    rc = lib.enarf_fine_sample(None, 0, 48, 48, 0, None, None, 0, 0, None, None, None)
+    rc = lib.enarf_fine_sample(None, 0, 48, 48, 0, None, None, 0, None, 0, None, None, None)
     assert rc == 1
 
 

