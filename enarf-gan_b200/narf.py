@@ -200,7 +200,19 @@ class TriPlaneNARF(nn.Module):
                                      feat_planes=planes[0], prob_planes=planes[1])
             return scene, planes, decoder
         if tri_plane is None:
+            tri_plane = model_input.get("planes")
+        if tri_plane is None:
             tri_plane = self.compute_tri_plane_feature(z, bone_length, model_input.get("truncation_psi", 1))
+        if isinstance(tri_plane, (tuple, list)):
+            # producer hand-off on the GAN path: a tri-plane generator whose last layer already writes the
+            # renderer's layout -- (feature planes (B,3,H,W,32) channels-last fp32 / bf16, probability planes (B,3P,H,W))
+            # -- so that neither the NCHW -> channels-last repack nor the gradient unpack runs, and the gradients come
+            # back in the same two layouts
+            feat, prob = tri_plane
+            self.buffers_tensors["tri_plane_feature"] = (feat, prob)
+            scene = ops.SceneBuffers(pose_scaled, cscale, self.canonical_pose, None, decoder,
+                                     feat_planes=feat.contiguous(), prob_planes=prob.to(torch.float32).contiguous())
+            return scene, (feat, prob), decoder
         tri_plane = tri_plane.to(torch.float32).contiguous()      # materialises an expanded constant plane
         self.buffers_tensors["tri_plane_feature"] = tri_plane      # narf.py:194
         if not self.training:

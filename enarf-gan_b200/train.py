@@ -67,7 +67,11 @@ def generator_loss(gen, dis, fake_img, fake_low_res_mask, bone_mask, cfg: StepCo
     total = loss_adv + loss_bone
     if cfg.tri_plane_reg_coef > 0:
         planes = _unwrap(gen).nerf.buffers_tensors["tri_plane_feature"]
-        total = total + planes.square().mean() * cfg.tri_plane_reg_coef
+        if isinstance(planes, (tuple, list)):      # handed over as (channels-last features, probabilities)
+            sq = sum(p.float().square().sum() for p in planes) / sum(p.numel() for p in planes)
+        else:
+            sq = planes.square().mean()
+        total = total + sq * cfg.tri_plane_reg_coef
     return total, {"adv_loss_gen": loss_adv.detach(), "bone_loss": loss_bone.detach()}
 
 

@@ -35,8 +35,11 @@ class PlaneProducer(nn.Module):
     """Stand-in for the StyleGAN2-ADA tri-plane generator: called as ``tri_plane_gen(z, c, truncation_psi=)`` with c the
     bone-length positional encoding (narf.py:286-289).  A learnable base plane set plus a per-sample low-rank term."""
 
-    def __init__(self, z_dim=512, c_dim=192, channels=168, res=256, rank=8):
+    def __init__(self, z_dim=512, c_dim=192, channels=168, res=256, rank=8, channels_last=False):
         super().__init__()
+        # channels_last: emit the renderer's own layout -- (B,3,H,W,32) feature planes + (B,72,H,W) probability planes
+        # (SURVEY 8f N1) -- instead of the reference's NCHW (B,168,H,W); the parameters are the same either way
+        self.channels_last = channels_last
         self.base = nn.Parameter(torch.randn(1, channels, res, res) * 0.5)
         self.to_code = nn.Sequential(nn.Linear(z_dim + c_dim, 256), nn.LeakyReLU(0.2), nn.Linear(256, channels * rank))
         self.basis = nn.Parameter(torch.randn(rank, res, res) * 0.1)
@@ -46,7 +49,13 @@ class PlaneProducer(nn.Module):
 
     def forward(self, z, c, truncation_psi=1):
         code = self.to_code(torch.cat([z, c], dim=1)).reshape(-1, self.channels, self.rank)
-        return self.base + torch.einsum("bcr,rhw->bchw", code, self.basis)
+        if not self.channels_last:
+            return self.base + torch.einsum("bcr,rhw->bchw", code, self.basis)
+        B, H, W = z.shape[0], self.base.shape[2], self.base.shape[3]
+        feat = self.base[:, :96].reshape(1, 3, 32, H, W).permute(0, 1, 3, 4, 2) \
+            + torch.einsum("bkcr,rhw->bkhwc", code[:, :96].reshape(B, 3, 32, self.rank), self.basis)
+        prob = self.base[:, 96:] + torch.einsum("bcr,rhw->bchw", code[:, 96:], self.basis)
+        return feat.contiguous(), prob
 
 
 class ConvDiscriminator(nn.Module):
@@ -72,13 +81,13 @@ class ConvDiscriminator(nn.Module):
         return self.head(x)
 
 
-def build(device, ert_eps=0.0):
+def build(device, ert_eps=0.0, channels_last=False):
     from enarf_gan_b200 import synthetic as S
     from enarf_gan_b200.generator import TriNARFGenerator
     cfg = dict(z_dim=256, background_ratio=0.3,
                nerf_params=dict(Nc=NC, Nf=NF, origin_location="center+head", coordinate_scale=3, render_bs=16384, ert_eps=ert_eps))
     gen = TriNARFGenerator(cfg, SIZE, num_bone=24, num_bone_param=23, parent_id=S.SMPL_PARENTS, black_background=True,
-                           tri_plane_gen=PlaneProducer())
+                           tri_plane_gen=PlaneProducer(channels_last=channels_last))
     gen.register_canonical_pose(S.canonical_pose())
     gen.nerf.rng_mode = "philox"
     return gen.to(device).train(), ConvDiscriminator(SIZE).to(device).train()
@@ -100,6 +109,7 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--n-accum", type=int, default=1)
+    ap.add_argument("--channels-last", action="store_true", help="producer emits the renderer's plane layout (no repack / unpack)")
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", 0), ("WORLD_SIZE", 1), ("LOCAL_RANK", 0)))
     torch.cuda.set_device(local)
@@ -109,7 +119,7 @@ def main():
     from enarf_gan_b200 import rendering, train
     lo, hi = rendering.shard_samples(a.global_batch, rank, world)
     B = hi - lo
-    gen, dis = build(device)
+    gen, dis = build(device, channels_last=a.channels_last)
     gen_ddp, dis_ddp = train.wrap_ddp(gen, device), train.wrap_ddp(dis, device)
     cfg = train.StepConfig(z_total=256 * 3, n_accum_step=a.n_accum, adv_loss_type="ce", tri_plane_reg_coef=0.0)
     go = torch.optim.Adam(gen_ddp.parameters(), lr=1e-4, betas=(0.0, 0.99))

@@ -66,3 +66,29 @@ def test_training_step_with_the_reference_discriminator():
     gen, _ = T.build(torch.device("cuda", 0))
     dis = Discriminator(H._EasyDict(minibatch_std=False), size=T.SIZE).cuda().train()
     _step(gen, dis, B=2)
+
+
+def test_channels_last_producer_hand_off_matches_nchw():
+    """SURVEY 8f N1, GAN half: a producer that emits (channels-last feature planes, probability planes) renders the
+    same image and receives the same parameter gradients as the NCHW producer with the same parameters -- without the
+    repack / unpack kernels."""
+    T = _script()
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    gen_a, _ = T.build(dev, channels_last=False)
+    gen_b, _ = T.build(dev, channels_last=True)
+    gen_b.load_state_dict(gen_a.state_dict())
+    d = T.synthetic_batch(0, 2, dev)
+    z = torch.randn(2, 768, device=dev)
+    outs = []
+    for gen in (gen_a, gen_b):
+        gen.nerf.rng_seed = 5
+        img, mask, _, _ = gen(d["pose_to_camera"], d["pose_to_world"], d["bone_length"], z, d["inv_intrinsics"])
+        ((img ** 2).mean() + ((1 - mask) ** 2).mean()).backward()
+        outs.append((img.detach(), mask.detach(), {k: p.grad.clone() for k, p in gen.named_parameters() if p.grad is not None}))
+    (ia, ma, ga), (ib, mb, gb) = outs
+    rel = lambda a, b: ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+    assert rel(ib, ia) < 1e-5 and rel(mb, ma) < 1e-5
+    assert set(ga) == set(gb)
+    for k in ga:
+        assert rel(gb[k], ga[k]) < 1e-4, k
