@@ -107,7 +107,14 @@ def mask_based_sampler(mask: torch.Tensor, ray_batchsize: int, generator: Option
     mask (B,h,w) -> (ray_idx (B,ray_bs) int64 flat pixel ids, homo_img (B,1,3,ray_bs) pixel centres)."""
     batchsize, h, w = mask.shape
     pad_size = 64
-    # a square max-pool is separable: two 1-D passes give the identical dilation at 2*129 instead of 129^2 taps
+    if mask.is_cuda:
+        # on the device: separable dilation + noise, exact radix select and the pixel centres in two small kernels
+        # (csrc/dso.cu).  The selected SET is torch.topk's for the same noise; rays come out in ascending pixel order.
+        from . import ops
+        noise = torch.empty(batchsize, h, w, device=mask.device).uniform_(generator=generator)
+        ray_idx, homo = ops.select_rays(mask, ray_batchsize, noise=noise, radius=pad_size)
+        return ray_idx, homo[:, None]
+    # CPU tensors (host-side tests): the same computation in torch.  A square max-pool is separable: two 1-D passes give the identical dilation at 2*129 instead of 129^2 taps
     m = torch.nn.functional.max_pool2d(mask.float()[:, None], (pad_size * 2 + 1, 1), stride=1, padding=(pad_size, 0))
     m = torch.nn.functional.max_pool2d(m, (1, pad_size * 2 + 1), stride=1, padding=(0, pad_size))[:, 0]
     m = m.reshape(batchsize, h * w)
@@ -209,6 +216,13 @@ class PhotometricLoss:
 
     def __call__(self, grid, sparse_color, sparse_mask, color, mask=None):
         batchsize, _, size, _ = color.shape
+        kind = _cfg(self.config, "nerf_loss_type")
+        if sparse_color.is_cuda and kind in ("mse", "mae"):
+            # fused gather + loss + gradients (csrc/dso.cu: enarf_photometric_loss)
+            from . import ops
+            lc, lm = ops.photometric_loss(grid, sparse_color, sparse_mask if mask is not None else None, color, mask, kind,
+                                          _cfg(self.config, "color_coef"), _cfg(self.config, "mask_coef"))
+            return lc, (lm if mask is not None else 0)
         sampled_color = torch.gather(color.reshape(batchsize, 3, size * size), 2, grid[:, None].expand(-1, 3, -1))
         sampled_mask = torch.gather(mask.reshape(batchsize, size * size), 1, grid) if mask is not None else None
         kind = _cfg(self.config, "nerf_loss_type")

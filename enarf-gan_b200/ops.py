@@ -409,3 +409,56 @@ def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None
     out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3,
                            (ert_eps, ert_hint, ert_stats, bg_const))
     return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
+
+
+# ---- DSO step around the renderer ------------------------------------------------------------------
+def select_rays(mask, ray_batchsize, noise=None, seed=0, radius=64):
+    """mask_based_sampler (libraries/NeRF/ray_sampler.py:7-39) on the device: dilate the (B,h,w) foreground mask by a
+    (2*radius+1)^2 max-pool, add U[0,1) noise (``noise`` (B,h,w) given, else in-kernel Philox keyed by ``seed``) and keep
+    the ``ray_batchsize`` best pixels of every image.  -> (ray_idx (B,k) int64 flat pixel ids in ascending order,
+    homo_img (B,3,k) pixel centres)."""
+    B, h, w = mask.shape
+    m = mask.to(torch.float32).contiguous()
+    scratch, score = torch.empty_like(m), torch.empty_like(m)
+    if noise is not None:
+        noise = noise.to(torch.float32).reshape(B, h, w).contiguous()
+    check(lib().enarf_ray_scores(ptr(m), B, h, w, int(radius), ptr(noise, allow_none=True), int(seed), ptr(scratch), ptr(score),
+                                 stream_ptr()))
+    idx = torch.empty(B, ray_batchsize, device=mask.device, dtype=torch.int64)
+    homo = torch.empty(B, 3, ray_batchsize, device=mask.device)
+    check(lib().enarf_select_rays(ptr(score), B, h * w, w, int(ray_batchsize), ptr(idx, torch.int64), ptr(homo), stream_ptr()))
+    return idx, homo
+
+
+class _PhotometricLoss(torch.autograd.Function):
+    """(colour loss, mask loss) of libraries/NeRF/loss.py:14-48 with the gather of the ground truth fused in; the
+    gradients with respect to the rendered colour / mask are produced by the same launch and scaled in the backward."""
+
+    @staticmethod
+    def forward(ctx, r_color, r_mask, gt_color, gt_mask, ray_idx, loss_type, color_coef, mask_coef):
+        B, _, k = r_color.shape
+        npix = gt_color.shape[-1] * gt_color.shape[-2] if gt_color.ndim == 4 else gt_color.shape[-1]
+        rc = r_color.detach().to(torch.float32).contiguous()
+        rm = r_mask.detach().to(torch.float32).contiguous() if r_mask is not None else None
+        gc = gt_color.detach().to(torch.float32).reshape(B, 3, npix).contiguous()
+        gm = gt_mask.detach().to(torch.float32).reshape(B, npix).contiguous() if gt_mask is not None else None
+        loss = torch.zeros(2, device=rc.device)
+        d_color = torch.empty_like(rc)
+        d_mask = torch.empty_like(rm) if gm is not None else None
+        check(lib().enarf_photometric_loss(ptr(rc), ptr(rm, allow_none=True), ptr(gc), ptr(gm, allow_none=True),
+                                           ptr(ray_idx.contiguous(), torch.int64), B, k, npix, int(loss_type), float(color_coef),
+                                           float(mask_coef), ptr(loss), ptr(d_color), ptr(d_mask, allow_none=True), stream_ptr()))
+        ctx.save_for_backward(d_color, d_mask if d_mask is not None else torch.empty(0, device=rc.device))
+        ctx.has_mask = d_mask is not None
+        return loss[0], loss[1]
+
+    @staticmethod
+    def backward(ctx, g_c, g_m):
+        d_color, d_mask = ctx.saved_tensors
+        return d_color * g_c, (d_mask * g_m if ctx.has_mask else None), None, None, None, None, None, None
+
+
+def photometric_loss(ray_idx, rendered_color, rendered_mask, gt_color, gt_mask, loss_type="mse", color_coef=1.0, mask_coef=1.0):
+    """-> (loss_color, loss_mask) as 0-d tensors (loss_mask is 0 when ``gt_mask`` is None)."""
+    code = {"mse": 0, "mae": 1}[loss_type]
+    return _PhotometricLoss.apply(rendered_color, rendered_mask, gt_color, gt_mask, ray_idx, code, color_coef, mask_coef)

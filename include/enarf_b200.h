@@ -177,6 +177,26 @@ int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, co
                           float* d_w1, float* d_w2, float* d_w3, float* d_b1, float* d_b2, float* d_b3, float ert_eps,
                           float bg_const, void* stream);
 
+/* ---- DSO step around the renderer ----------------------------------------------------------------
+ * mask_based_sampler (libraries/NeRF/ray_sampler.py:7-39) in two calls.
+ * enarf_ray_scores: score = max_pool2d(mask, 2*radius+1, stride 1, padding radius) + U[0,1) per pixel.  mask, scratch,
+ * score (B,h,w) fp32; noise (B,h,w) caller-drawn uniforms, or NULL for in-kernel Philox keyed by `seed`. */
+int enarf_ray_scores(const float* mask, int B, int h, int w, int radius, const float* noise, uint64_t seed,
+                     float* scratch, float* score, void* stream);
+/* enarf_select_rays: the k largest scores of every image (torch.topk(..., sorted=False): the SET is exact, ties at
+ * the threshold go to the lower pixel index; output in ascending pixel order).  score (B,n); idx_out (B,k) int64 flat
+ * pixel ids; homo_out (B,3,k), optional: pixel centres (x + .5, y + .5, 1) with x = id % width, y = id / width. */
+int enarf_select_rays(const float* score, int B, int n, int width, int k, int64_t* idx_out, float* homo_out,
+                      void* stream);
+/* PhotometricLoss (libraries/NeRF/loss.py:14-48) fused: gather of the ground truth at ray_idx, colour loss
+ * (loss_type 0: MSE, 1: mean of max(|diff|, 0.01)) x color_coef, mask MSE x mask_coef (gt_mask NULL: skipped).
+ * rendered_color (B,3,k), rendered_mask (B,k), gt_color (B,3,npix), gt_mask (B,npix), ray_idx (B,k) int64.
+ * loss[0] += colour loss, loss[1] += mask loss (caller zeroes); d_color (B,3,k) / d_mask (B,k), optional: the
+ * gradients of those two numbers with respect to the rendered colour / mask. */
+int enarf_photometric_loss(const float* rendered_color, const float* rendered_mask, const float* gt_color,
+                           const float* gt_mask, const int64_t* ray_idx, int B, int k, int npix, int loss_type,
+                           float color_coef, float mask_coef, float* loss, float* d_color, float* d_mask, void* stream);
+
 /* Point query = calc_density_and_color_from_camera_coord_v2 (models/narf.py:176-211): points (B,3,N) in
  * the scaled camera frame -> density (B,1,N), color (B,3,N) (NULL to skip), part_mask (B,N) uint32 bit p =
  * part p valid (NULL to skip). */
