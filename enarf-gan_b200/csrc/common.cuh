@@ -6,6 +6,16 @@
 
 #include "../../include/enarf_b200.h"
 
+// Development build (ENARF_NVCC_EXTRA=-DENARF_DEBUG_BOUNDS): device-side asserts on the indices that address shared
+// and global memory (compute-sanitizer is not available on the GPU pool this library is developed on).  A failed
+// assert traps the kernel; the next ABI call / synchronisation reports the CUDA error.
+#ifdef ENARF_DEBUG_BOUNDS
+#include <assert.h>
+#define ENARF_DBG_ASSERT(c) assert(c)
+#else
+#define ENARF_DBG_ASSERT(c) ((void)0)
+#endif
+
 #define FEAT ENARF_FEAT_DIM
 #define HID ENARF_HIDDEN
 #define N_PROBE 32  // depth probes per ray (reference: libraries/NeRF/rendering.py:18)

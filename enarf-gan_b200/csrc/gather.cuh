@@ -41,6 +41,7 @@ __device__ __forceinline__ void gather_pair(float4& f, const T* __restrict__ fea
     float4 v[12];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
+        ENARF_DBG_ASSERT((off[k] & 31u) == 0u);     // a texel offset is a multiple of the 32 channels
         const T* p0 = feat + off[k];
         const T* p1 = p0 + row_elems;
         v[4 * k + 0] = load_feat4(p0);

@@ -158,6 +158,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                         base = atomicAdd(a.ck.cursor, np_tile);
                         if ((long long)base + np_tile > a.ck.capacity) base = -1;
                     }
+                    ENARF_DBG_ASSERT(base < 0 || (long long)base + np_tile <= a.ck.capacity);
                     a.ck.tile_base[tile] = base;
                     s.t.pad_[1] = base;
                 }
@@ -172,6 +173,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                 const int a0 = n_done + 32 * c;
                 if (a0 >= n_active) break;
                 const int np = min(32, n_active - a0);
+                ENARF_DBG_ASSERT(a0 >= 0 && n_active <= TP_MAX);
                 const int tb = (MODE == MODE_FINE && a.ck.rec) ? s.t.pad_[1] : -1;
                 gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane,
                                  tb >= 0 ? a.ck.rec + (size_t)tb * REC : nullptr, tb >= 0 ? a.ck.feat + (size_t)tb * FEAT : nullptr

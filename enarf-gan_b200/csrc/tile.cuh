@@ -260,7 +260,9 @@ __device__ __forceinline__ void tile_compact(TileSmem& t, int rays, int S, int K
         for (int k = 0; k < (q >> 5); ++k) base += __popc(bits[k]);
         if ((bal >> lane) & 1) {
             int rr;
+            ENARF_DBG_ASSERT(base + __popc(bal & ((1u << lane) - 1)) < TP_MAX);
             t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)(direct ? q : point_of(q, rr));
+            ENARF_DBG_ASSERT((direct ? q : point_of(q, rr)) < rays * S);
         }
         if (q + 32 >= cnt32 && lane == 0) t.n_active = base + __popc(bal);   // the last block closes the count
     }
@@ -449,6 +451,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
             uint32_t m = __float_as_uint(pm.w);
             for (int k = target - t.pref[lo]; k > 0; --k) m &= m - 1;
             const int p = __ffs(m) - 1;
+            ENARF_DBG_ASSERT(p >= 0 && p < sc.P && r < RECW);
             float c[3];
             part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
             Bilin bl[3];
@@ -456,6 +459,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
+                ENARF_DBG_ASSERT(bl[k].x0 >= 0 && bl[k].x0 <= W - 2 && bl[k].y0 >= 0 && bl[k].y0 <= H - 2);
                 sg[k] = sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
                 wp *= sg[k];
             }
@@ -470,6 +474,7 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
 #pragma unroll
             for (int k = 0; k < 4; ++k) dst[k] = rw[k];
             if (ck_rec) {
+                ENARF_DBG_ASSERT(target >= 0);
                 // streaming stores: the checkpoint is written once and must not push the planes out of L2
                 float4* g = reinterpret_cast<float4*>(ck_rec + (size_t)target * REC);
 #pragma unroll
