@@ -40,6 +40,7 @@ _SIGNATURES = {
     "enarf_warp_planes_fwd": (c_int, [_P, _P, c_int, c_int, c_int, _P, c_int, _P]),
     "enarf_warp_planes_bwd": (c_int, [_P, c_int, _P, _P, c_int, c_int, c_int, _P, _P, _P]),
     "enarf_ray_scores": (c_int, [_P, c_int, c_int, c_int, c_int, _P, c_uint64, _P, _P, _P]),
+    "enarf_ray_scores_static": (c_int, [_P, c_int, c_int, c_int, c_int, _P, c_uint64, _P, _P]),
     "enarf_select_rays": (c_int, [_P, c_int, c_int, c_int, c_int, _P, _P, _P]),
     "enarf_photometric_loss": (c_int, [_P, _P, _P, _P, _P, c_int, c_int, c_int, c_int, c_float, c_float, _P, _P, _P, _P]),
     "enarf_near_far": (c_int, [_P, c_int, c_int, c_float, c_float, _P, _P]),

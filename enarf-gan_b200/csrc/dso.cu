@@ -59,6 +59,58 @@ extern "C" int enarf_ray_scores(const float* mask, int B, int h, int w, int radi
     return ENARF_OK;
 }
 
+// ---- the same score image for callers that cannot allocate -------------------------------------------------
+// enarf_ray_scores_static: enarf_ray_scores with the row-pass scratch in a file-scope device array instead of a caller
+// buffer (no counterpart in the reference; added for callers that cannot call
+// cudaMalloc: CUDA-graph capture, tight serving loops).  Every GPU that loads the library holds the 4 MB until exit.
+// The array's name is only a host-side stand-in in host code: its device address is resolved once per device with
+// cudaGetSymbolAddress (with that device current) and cached.  No cudaMalloc / cudaFree / allocating library call.
+// The row pass overwrites every element the column pass reads (B*h*w floats), so nothing has to start at zero; all
+// calls share the one array, so two calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) float g_score_scratch[ENARF_STATIC_SCRATCH_FLOATS];
+
+static float* score_scratch_ptr(const char* who) {
+    static float* cached[64] = {};      // per device id; benign race: concurrent first calls store the same address
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        enarf_set_error("%s: cudaGetDevice: %s", who, cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (dev >= 0 && dev < 64) {
+        float* p = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+        if (p) return p;
+    }
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_score_scratch);
+    if (e != cudaSuccess || !p) {
+        enarf_set_error("%s: cudaGetSymbolAddress(g_score_scratch) on device %d: %s", who, dev, cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (dev >= 0 && dev < 64) __atomic_store_n(&cached[dev], p, __ATOMIC_RELEASE);
+    return p;
+}
+
+extern "C" int enarf_ray_scores_static(const float* mask, int B, int h, int w, int radius, const float* noise,
+                                       uint64_t seed, float* score, void* stream) {
+    ENARF_REQUIRE(mask && score && B > 0 && h > 0 && w > 0 && radius >= 0, ENARF_ERR_INVALID_ARG,
+                  "enarf_ray_scores_static: bad arguments");
+    ENARF_REQUIRE(w <= 8192, ENARF_ERR_UNSUPPORTED, "enarf_ray_scores_static: width %d exceeds 8192", w);
+    const long long need = (long long)B * h * w;
+    ENARF_REQUIRE(need <= (long long)ENARF_STATIC_SCRATCH_FLOATS, ENARF_ERR_UNSUPPORTED,
+                  "enarf_ray_scores_static: B*h*w = %lld floats exceeds the static scratch of %d floats "
+                  "(ENARF_STATIC_SCRATCH_FLOATS); use enarf_ray_scores with a caller buffer", need,
+                  ENARF_STATIC_SCRATCH_FLOATS);
+    float* scratch = score_scratch_ptr("enarf_ray_scores_static");
+    if (!scratch) return ENARF_ERR_CUDA;
+    cudaStream_t st = (cudaStream_t)stream;
+    dilate_rows_kernel<<<B * h, 256, (size_t)w * sizeof(float), st>>>(mask, h, w, radius, scratch);
+    ENARF_CHECK_LAUNCH("enarf_ray_scores_static");
+    dilate_cols_kernel<<<dim3((w + 255) / 256, h, B), 256, 0, st>>>(scratch, noise, seed, noise ? 0 : 1, h, w, radius, score);
+    ENARF_CHECK_LAUNCH("enarf_ray_scores_static");
+    return ENARF_OK;
+}
+
 // ---- exact top-k selection ----------------------------------------------------------------------------------
 // One 1024-thread CTA per image.  Scores are finite floats; the map below makes unsigned order equal float order.
 __device__ __forceinline__ uint32_t order_key(float f) {

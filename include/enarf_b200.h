@@ -183,6 +183,18 @@ int enarf_render_fine_bwd(const enarf_scene_t* scene, const float* depth_min, co
  * score (B,h,w) fp32; noise (B,h,w) caller-drawn uniforms, or NULL for in-kernel Philox keyed by `seed`. */
 int enarf_ray_scores(const float* mask, int B, int h, int w, int radius, const float* noise, uint64_t seed,
                      float* scratch, float* score, void* stream);
+/* enarf_ray_scores_static: enarf_ray_scores for callers that cannot allocate device memory (code under CUDA-graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same inputs, same `score` output, bit-identical results; the row-pass scratch is a
+ * file-scope `static __device__ __align__(256)` array inside the library (ENARF_STATIC_SCRATCH_FLOATS floats = 4 MB,
+ * held by every GPU that loads the library until the process exits), its device address resolved once per device with
+ * cudaGetSymbolAddress.  The call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).
+ * B*h*w > ENARF_STATIC_SCRATCH_FLOATS returns ENARF_ERR_UNSUPPORTED with a message naming the limit.  The array is
+ * shared by every call and keeps the last call's contents (each call overwrites all it reads, nothing needs
+ * clearing): calls that overlap on the GPU -- different streams, no ordering between them -- race on it. */
+#define ENARF_STATIC_SCRATCH_FLOATS (1 << 20)   /* e.g. four 512 x 512 masks (BASELINE configs[3]) */
+int enarf_ray_scores_static(const float* mask, int B, int h, int w, int radius, const float* noise, uint64_t seed,
+                            float* score, void* stream);
 /* enarf_select_rays: the k largest scores of every image (torch.topk(..., sorted=False): the SET is exact, ties at
  * the threshold go to the lower pixel index; output in ascending pixel order).  score (B,n); idx_out (B,k) int64 flat
  * pixel ids; homo_out (B,3,k), optional: pixel centres (x + .5, y + .5, 1) with x = id % width, y = id / width. */
