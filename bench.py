@@ -207,14 +207,19 @@ def step_device(w, step_idx, timer=None, world=None):
 def mean_valid_parts(w):
     """v-bar of SURVEY.md 8(d): mean number of valid parts per point, for the coarse and the fine samples."""
     from enarf_gan_b200 import ops
+    dbg = (lambda tag: (torch.cuda.synchronize(), print("[dbg] ok:", tag, file=sys.stderr))) if os.environ.get("ENARF_BENCH_DEBUG_SYNC") else (lambda tag: None)
+    dbg("entry")
     scene = ops.SceneBuffers(w["pose"], w["cscale"], w["canon"], w["tri_plane"], w["decoder"])
+    dbg("repack")
     _, _, _, _, bins, dmin, dmax, direction = w["last"]
     out = []
     cb = (torch.arange(NC, device=bins.device) + 0.5) / NC
     for u in (cb[None, None].expand(w["B"], w["n"], NC), bins):
         start, end = dmin[:, None] * direction, dmax[:, None] * direction
         pts = (start[..., None] * (1 - u[:, None]) + end[..., None] * u[:, None]).reshape(w["B"], 3, -1).contiguous()
+        dbg("pts")
         _, _, m = ops.density_query(scene, pts, want_color=False, want_mask=True)
+        dbg("query")
         cnt = torch.zeros_like(m)
         for p in range(PARTS):
             cnt += (m >> p) & 1

@@ -73,6 +73,8 @@ struct __align__(16) TileSmem {
     int n_active;
     int tile;
     int pad_[2];
+    int n_next;                        // tile_compact: the list length being built (published as n_active after a barrier)
+    int pad2_[3];
 };
 
 // Early ray termination (north_star step (e)): the samples of a ray are evaluated front to back in groups
@@ -264,11 +266,15 @@ __device__ __forceinline__ void tile_compact(TileSmem& t, int rays, int S, int K
             t.list[base + __popc(bal & ((1u << lane) - 1))] = (uint16_t)(direct ? q : point_of(q, rr));
             ENARF_DBG_ASSERT((direct ? q : point_of(q, rr)) < rays * S);
         }
-        if (q + 32 >= cnt32 && lane == 0) t.n_active = base + __popc(bal);   // the last block closes the count
+        // the last block closes the count -- into n_next, NOT n_active: a warp that is late entering this function
+        // (the point query stores its part masks to global memory just before) must still read the old n_active as n0
+        if (q + 32 >= cnt32 && lane == 0) t.n_next = base + __popc(bal);
     }
+    if (cnt32 == 0 && tid == 0) t.n_next = n0;
     __syncthreads();
     // exclusive prefix of pairs-per-point over the new list entries (2 entries per thread)
-    const int na = t.n_active - n0;
+    const int na = t.n_next - n0;
+    if (tid == 0) t.n_active = n0 + na;      // visible to every thread after the two barriers below
     const int p_base = n0 ? t.pref[n0] : 0;
     const int i0 = 2 * tid;
     const int c0 = i0 < na ? __popc(__float_as_uint(t.pm[t.list[n0 + i0]].w)) : 0;
