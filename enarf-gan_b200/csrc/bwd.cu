@@ -11,10 +11,11 @@
 //   1. positions + part masks are regenerated with the forward's contract arithmetic (bit-identical masks);
 //   2. one warp per ray turns the upstream gradients and the forward's saved (rgb, sigma) into per-sample
 //      d/d rgb and d/d sigma (two shuffle scans: transmittance prefix, weighted-gradient suffix), in place;
-//   3. per chunk of <= 128 active points: pair records -> gather -> decoder forward (activations kept as
-//      [channel][point] rows) -> head backward -> G2 -> dW2 -> G1 -> dW1 -> dX, all as register-tiled FP32
-//      GEMMs; the weight gradients are accumulated in registers over the CTA's whole lifetime and flushed
-//      with atomics once per (CTA, sample);
+//   3. per chunk of <= 64 active points / 160 pairs: pair records (the forward's checkpoint, fetched by one TMA bulk
+//      copy, or rebuilt) -> features (checkpoint rows, or gathered) -> decoder forward (activations kept as
+//      [channel][point] rows) -> head backward -> G2 -> dW2 -> G1 -> dW1 -> dX, all six GEMMs as error-compensated
+//      3xTF32 mma.sync from shared-memory fragments; the weight gradients are accumulated in registers over the
+//      CTA's whole lifetime and flushed with atomics once per (CTA, sample);
 //   4. d(feature) is scattered with 128-bit vector reductions (red.global.add.v4.f32) into the channels-last
 //      gradient planes using the same pair records; d(part weight) goes through the sigmoid product into
 //      scalar reductions on the probability planes.
@@ -27,6 +28,12 @@
 #include "mma_smem.cuh"
 
 #define PBLK (CH / 32)        // 32-point blocks per chunk
+// d(features) of a chunk is handed to the scatter as [point][DXS] rows (the dead G2 buffer): the 8 lanes of a pair read
+// one 128-bit word each -- 128 contiguous bytes, conflict-free -- and the mma epilogue's 64-bit stores are conflict-free
+// with a row stride of 40 words (8 g + 2 t covers the 32 banks once per half warp).  The [channel][point] form it
+// replaces cost four 4-way-conflicting 32-bit loads per lane: 34 % of the kernel's excess shared-memory wavefronts.
+#define DXS 40
+static_assert(CH * DXS <= HID * AS, "dX rows fit the G2 buffer");
 #define WCOL (NWARP / 4)      // column groups of the weight-gradient tiles (4 row blocks of 16 outs each)
 #define TN2 (8 / WCOL)        // 8-column mma tiles per warp: dW2 (64 columns) / dW1 (32 columns)
 #define TN1 (4 / WCOL)
@@ -64,6 +71,7 @@ struct __align__(16) BwdSmem {
     float4 pg[TP_MAX];       // forward (r,g,b,sigma), overwritten by d/d(r,g,b,sigma)
     float rg[MAX_RAYS * 8];  // upstream d/d(color rgb, mask, disparity) per ray
     float db3[4];
+    unsigned long long rec_bar;   // mbarrier of the records' bulk copy
 };
 
 #ifdef ENARF_PHASE_TIMING   // development build: per-phase clock64() sums of thread 0 of every CTA
@@ -84,6 +92,28 @@ extern "C" int enarf_debug_bwd_phases(unsigned long long* host_out, int reset) {
 #define PHASE(i)
 #define PHASE_FLUSH
 #endif
+
+// ---- TMA 1-D bulk copy (cp.async.bulk) of a contiguous global range into shared memory, completion on an mbarrier --
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, uint32_t bytes, unsigned long long* bar) {
+    const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    // the destination was last touched through the generic proxy (the previous chunk's scatter read it)
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(dst_smem)),
+                 "l"(src), "r"(bytes), "r"(b)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    const uint32_t b = (uint32_t)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(b), "r"(parity) : "memory");
+}
 
 __device__ __forceinline__ float act_grad(float a) { return (a > 0.f ? 1.f : 0.2f) * 1.4142135623730951f; }
 
@@ -260,8 +290,7 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
                 v[(4 * k + 3) % (CK ? 1 : 12)] = load_feat4(t1 + FEAT);
             }
         }
-        const float* src = X + (lane8 * 4) * AS + q;
-        const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
+        const float4 dx = *reinterpret_cast<const float4*>(X + q * DXS + 4 * lane8);
         const float4 dxw = CK ? dx : make_float4(dx.x * wp, dx.y * wp, dx.z * wp, dx.w * wp);
         // the reductions depend only on the weights and dX: they are issued while the texel loads are still in flight
         float w[12];
@@ -336,9 +365,9 @@ __device__ __forceinline__ void scatter_chunk_merged(const TileSmem& t, const fl
         const float* rw = rec + r * REC;
         const float4 v = __ldg(reinterpret_cast<const float4*>(ck_feat + (size_t)r * FEAT + 4 * lane8));
         const int q = (__float_as_int(rw[3]) >> 8) - c0;
-        const float* src = X + (lane8 * 4) * AS + q;
+        const float4 dxa = *reinterpret_cast<const float4*>(X + q * DXS + 4 * lane8);
         const float inv_wp = rw[16];
-        float fdot = ((v.x * src[0] + v.y * src[AS]) + (v.z * src[2 * AS] + v.w * src[3 * AS])) * inv_wp;
+        float fdot = ((v.x * dxa.x + v.y * dxa.y) + (v.z * dxa.z + v.w * dxa.w)) * inv_wp;
         fdot += __shfl_xor_sync(gmask, fdot, 1);
         fdot += __shfl_xor_sync(gmask, fdot, 2);
         fdot += __shfl_xor_sync(gmask, fdot, 4);
@@ -399,8 +428,7 @@ __device__ __forceinline__ void scatter_chunk_merged(const TileSmem& t, const fl
             const int p = w3 & 255, q = (w3 >> 8) - c0;
             ENARF_DBG_ASSERT(q >= 0 && q < CH && p < sc.P);
             const float4 w4 = *reinterpret_cast<const float4*>(rw + 4 + 4 * k);
-            const float* src = X + (lane8 * 4) * AS + q;
-            const float4 dx = make_float4(src[0], src[AS], src[2 * AS], src[3 * AS]);
+            const float4 dx = *reinterpret_cast<const float4*>(X + q * DXS + 4 * lane8);
             fma4(acc[0], w4.x, dx);
             fma4(acc[1], w4.y, dx);
             fma4(acc[2], w4.z, dx);
@@ -444,6 +472,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
     WGrad wg;
     wgrad_zero(wg);
     if (tid < 4) s.db3[tid] = 0.f;
+    if (tid == 0) {
+        mbar_init(&s.rec_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    uint32_t rec_phase = 0;      // parity of the next completion of rec_bar (uniform across the CTA)
     PHASE_DECL;
 
     for (;;) {
@@ -594,15 +627,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             const bool tile_on = 32 * m.pb < cnt;   // this warp's 32 points intersect the chunk
             const int pair0 = s.t.pref[c0];
             if (tb >= 0) {   // records straight from the forward's checkpoint (5 x 128 bit each, coalesced)
-                const float4* src = reinterpret_cast<const float4*>(a.ck.rec + (size_t)(tb + pair0) * REC);
-                float4* dst = reinterpret_cast<float4*>(s.r.rec);
-                const int nq = (s.t.pref[c1] - pair0) * (REC / 4);
-                // asynchronous copy: the records are only needed by the scatter at the end of the chunk
-                for (int e = tid; e < nq; e += NT)
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + e)),
-                                 "l"(src + e)
-                                 : "memory");
-                asm volatile("cp.async.commit_group;" ::: "memory");
+                // one TMA bulk copy, issued by one thread and awaited only before the scatter at the end of the chunk (the
+                // GEMM phases run under it); it replaced ~3 16-byte cp.async per thread and their shared-memory wavefronts
+                if (tid == 0)
+                    bulk_load(s.r.rec, a.ck.rec + (size_t)(tb + pair0) * REC,
+                              (uint32_t)((s.t.pref[c1] - pair0) * REC * sizeof(float)), &s.rec_bar);
             } else {
                 setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             }
@@ -703,21 +732,22 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             // dW1 += G1^T X: warp tile rows (o) 16 wr.., cols (c) 8 TN1 wc..
             wgrad_mma<TN1, FASTG>(s.A1, s.X, 16 * m.wr, 8 * TN1 * m.wc, cend, m.g, m.t, wg.w1);
             // no barrier: dX goes to the rows of A2 (G2 is dead after the G1 phase), so X and G1 are only read here
-            if (tile_on) {   // dX = G1 W1 -> A2 rows 0..31: warp tile points 32 pb.., channels 8 ob..
+            if (tile_on) {   // dX = G1 W1 -> the G2 buffer as [point][DXS]: warp tile points 32 pb.., channels 8 ob..
                 float acc[2][1][4];
                 gemm_pts_mma<HID, 1, true, FASTG>(s.A1, s.dec.w1, W1S, 32 * m.pb, 8 * m.ob, m.g, m.t, acc);
                 const int col = 8 * m.ob + 2 * m.t;
 #pragma unroll
                 for (int mt = 0; mt < 2; ++mt) {
-                    float* d0 = s.A2 + col * AS + 32 * m.pb + 16 * mt + m.g;
-                    d0[0] = acc[mt][0][0];
-                    d0[AS] = acc[mt][0][1];
-                    d0[8] = acc[mt][0][2];
-                    d0[AS + 8] = acc[mt][0][3];
+                    float* d0 = s.A2 + (32 * m.pb + 16 * mt + m.g) * DXS + col;
+                    *reinterpret_cast<float2*>(d0) = make_float2(acc[mt][0][0], acc[mt][0][1]);
+                    *reinterpret_cast<float2*>(d0 + 8 * DXS) = make_float2(acc[mt][0][2], acc[mt][0][3]);
                 }
             }
-            if (tb >= 0) asm volatile("cp.async.wait_group 0;" ::: "memory");   // this chunk's records have landed
             __syncthreads();
+            if (tb >= 0) {   // this chunk's records have landed (every thread observes the barrier phase itself)
+                mbar_wait(&s.rec_bar, rec_phase);
+                rec_phase ^= 1u;
+            }
             PHASE(11);  // dX
             const int c1n = c1 < n_active ? chunk_end(s.t, c1) : c1;
             if (a.feat && c1 < n_active) load_rows(c1, c1n - c1);   // next chunk's rows, in flight during the scatter

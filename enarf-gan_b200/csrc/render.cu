@@ -166,13 +166,15 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             }
             WarpSlab& my = s.u.slab[warp];
             const int g = lane >> 2, t4 = lane & 3;
+            const int csz = 32;   // (an eighth of the round's active points per chunk, so that no warp idles at the tile-end
+                                  // barrier, measured no faster: profiles/micro_opt_r2.txt)
             for (;;) {
                 int c = 0;
                 if (lane == 0) c = atomicAdd(&s.t.pad_[0], 1);
                 c = __shfl_sync(0xffffffffu, c, 0);
-                const int a0 = n_done + 32 * c;
+                const int a0 = n_done + csz * c;
                 if (a0 >= n_active) break;
-                const int np = min(32, n_active - a0);
+                const int np = min(csz, n_active - a0);
                 ENARF_DBG_ASSERT(a0 >= 0 && n_active <= TP_MAX);
                 const int tb = (MODE == MODE_FINE && a.ck.rec) ? s.t.pad_[1] : -1;
                 gather32_warp<T>(s.t, my.rec, my.X, s.part, sc, b, a0, np, lane,
