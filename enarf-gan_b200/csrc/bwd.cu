@@ -33,6 +33,11 @@
 // with a row stride of 40 words (8 g + 2 t covers the 32 banks once per half warp).  The [channel][point] form it
 // replaces cost four 4-way-conflicting 32-bit loads per lane: 34 % of the kernel's excess shared-memory wavefronts.
 #define DXS 40
+// Pair budget of a chunk.  The record buffer holds PB pairs; with the forward's checkpoint the records beyond PB are fetched
+// into the G1 buffer once it is dead (after the dW1 / dX phase), so a chunk is its 64 points (3.6 pairs per point on the
+// bench batch) instead of the ~45 points whose pairs fit PB: a quarter fewer chunks, i.e. of everything that costs per chunk
+// (six GEMM phases on 64-row tiles, the head, eight barriers).
+#define PBX ((HID * AS / REC) & ~7)
 static_assert(CH * DXS <= HID * AS, "dX rows fit the G2 buffer");
 #define WCOL (NWARP / 4)      // column groups of the weight-gradient tiles (4 row blocks of 16 outs each)
 #define TN2 (8 / WCOL)        // 8-column mma tiles per warp: dW2 (64 columns) / dW1 (32 columns)
@@ -71,7 +76,7 @@ struct __align__(16) BwdSmem {
     float4 pg[TP_MAX];       // forward (r,g,b,sigma), overwritten by d/d(r,g,b,sigma)
     float rg[MAX_RAYS * 8];  // upstream d/d(color rgb, mask, disparity) per ray
     float db3[4];
-    unsigned long long rec_bar;   // mbarrier of the records' bulk copy
+    unsigned long long rec_bar[2];   // mbarriers of the records' bulk copies: first PB pairs, overflow
 };
 
 #ifdef ENARF_PHASE_TIMING   // development build: per-phase clock64() sums of thread 0 of every CTA
@@ -257,8 +262,11 @@ __device__ __forceinline__ void decoder_layer(const float* src, const float* Wm,
 // CK: the records come from the forward's pair checkpoint (weights already multiplied by the part weight, word 3 =
 // part | active index << 8, word 16 = 1 / part weight) and ck_feat points at the chunk's first checkpointed pair
 // feature, which replaces the 12 texel loads: <dX, f_p> = <dX, wp f_p> / wp.
+// Records [0, PB) of the chunk are in `rec`; with the checkpoint a chunk may hold up to PB + PBX pairs, the rest sit in
+// `rec_x` (the dead G1 buffer), fetched by a second bulk copy that completes on `bar_x` (parity `phase_x`).
 template <typename T, bool CK>
-__device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* rec, const float* X, const BwdArgs& a,
+__device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* rec, const float* rec_x,
+                                              unsigned long long* bar_x, uint32_t phase_x, const float* X, const BwdArgs& a,
                                               int b, int c0, int c1, int tid, const float* __restrict__ ck_feat) {
     const enarf_scene_t& sc = a.sc;
     const int lane8 = tid & 7, npairs = t.pref[c1] - t.pref[c0];
@@ -267,8 +275,13 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
     const T* feat = reinterpret_cast<const T*>(sc.feat_planes) + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dfeat = a.d_feat + (size_t)b * 3 * HW * FEAT + lane8 * 4;
     float* dprob = a.d_prob + (size_t)b * a.d_prob_stride;
+    bool waited = false;
     for (int r = tid >> 3; r < npairs; r += NT / 8) {
-        const float* rw = rec + r * REC;
+        if (CK && r >= PB && !waited) {   // the overflow records have landed (each thread observes the barrier itself)
+            mbar_wait(bar_x, phase_x);
+            waited = true;
+        }
+        const float* rw = (CK && r >= PB) ? rec_x + (r - PB) * REC : rec + r * REC;
         const float4* rp = reinterpret_cast<const float4*>(rw);
         const float4 o4 = rp[0];
         const unsigned off[3] = {__float_as_uint(o4.x), __float_as_uint(o4.y), __float_as_uint(o4.z)};
@@ -333,127 +346,6 @@ __device__ __forceinline__ void scatter_chunk(const TileSmem& t, const float* re
     }
 }
 
-// ---- merged scatter (pair checkpoint path) -----------------------------------------------------------------------
-// Measured on the bench workload (scripts/dup_texels.py, profiles/dup_texels_r2.txt): 77 % of a tile's 128-B line
-// updates hit a line the same tile has already touched -- consecutive fine samples of a ray sit a fraction of a texel
-// apart -- and even among 12 consecutive pairs a third of the bilinear footprints are identical.  Reductions are what
-// bounds this phase (the L2 retires ~49 G lines/s chip-wide whichever way they are issued: scripts/microbench/
-// bulk_red.cu), so each warp merges the footprints of its own window of pairs before it touches global memory:
-//   pass A  (8 lanes per pair)  d w_p = <dX, f_p> from the checkpointed pair feature -> shared memory;
-//   pass B  the warp's (pair, plane) entries -- <= 60 -- are sorted by texel in registers (64-key bitonic network,
-//           shuffles only); a run of equal texels = one footprint; the four 8-lane groups walk the runs, accumulate the
-//           four corners' 32-channel contributions in registers and issue 4 red.v4 per RUN instead of per entry; the
-//           probability-plane reductions are merged the same way per (part, footprint).
-// Scratch: fdot_s[PB] floats and srt[NWARP][64] words in dead activation rows.
-#define PWMAX ((PB + NWARP - 1) / NWARP)
-static_assert(3 * PWMAX <= 64, "a warp's (pair, plane) entries fit the 64-key sort");
-__device__ __forceinline__ void scatter_chunk_merged(const TileSmem& t, const float* rec, const float* X, const BwdArgs& a,
-                                                     int b, int c0, int c1, int tid, const float* __restrict__ ck_feat,
-                                                     float* fdot_s, uint32_t* srt_all) {
-    const enarf_scene_t& sc = a.sc;
-    const int lane = tid & 31, warp = tid >> 5, lane8 = tid & 7, grp = lane >> 3;
-    const int npairs = t.pref[c1] - t.pref[c0];
-    const int H = sc.H, W = sc.W, HW = H * W;
-    const unsigned gmask = 0xffu << (tid & 24);
-    float* dfeat = a.d_feat + (size_t)b * 3 * HW * FEAT + lane8 * 4;
-    float* dprob = a.d_prob + (size_t)b * a.d_prob_stride;
-    const int pw = (npairs + NWARP - 1) / NWARP;                 // pairs per warp window
-    const int p0 = min(npairs, warp * pw), p1 = min(npairs, p0 + pw);
-    uint32_t* srt = srt_all + warp * 64;
-    // ---- pass A: d w_p of the warp's own pairs ----
-    for (int r = p0 + grp; r < p1; r += 4) {
-        const float* rw = rec + r * REC;
-        const float4 v = __ldg(reinterpret_cast<const float4*>(ck_feat + (size_t)r * FEAT + 4 * lane8));
-        const int q = (__float_as_int(rw[3]) >> 8) - c0;
-        const float4 dxa = *reinterpret_cast<const float4*>(X + q * DXS + 4 * lane8);
-        const float inv_wp = rw[16];
-        float fdot = ((v.x * dxa.x + v.y * dxa.y) + (v.z * dxa.z + v.w * dxa.w)) * inv_wp;
-        fdot += __shfl_xor_sync(gmask, fdot, 1);
-        fdot += __shfl_xor_sync(gmask, fdot, 2);
-        fdot += __shfl_xor_sync(gmask, fdot, 4);
-        if (lane8 == 0) fdot_s[r] = fdot;
-    }
-    // ---- pass B: sort the window's (pair, plane) entries by texel ----
-    const int nent = 3 * (p1 - p0);
-    uint32_t k0 = 0xffffffffu, k1 = 0xffffffffu;
-    if (lane < nent) {
-        const int pi = lane / 3, k = lane - 3 * pi;
-        k0 = ((__float_as_uint(rec[(p0 + pi) * REC + k]) >> 5) << 6) | (uint32_t)pi;
-    }
-    if (lane + 32 < nent) {
-        const int pi = (lane + 32) / 3, k = lane + 32 - 3 * pi;
-        k1 = ((__float_as_uint(rec[(p0 + pi) * REC + k]) >> 5) << 6) | (uint32_t)pi;
-    }
-#pragma unroll
-    for (int k = 2; k <= 64; k <<= 1) {
-#pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j == 32) {
-                const uint32_t lo = min(k0, k1), hi = max(k0, k1);
-                k0 = lo;
-                k1 = hi;
-            } else {
-                const uint32_t q0 = __shfl_xor_sync(0xffffffffu, k0, j), q1 = __shfl_xor_sync(0xffffffffu, k1, j);
-                const bool lower = (lane & j) == 0;
-                const bool up0 = (lane & k) == 0, up1 = ((lane + 32) & k) == 0;
-                k0 = (lower == up0) ? min(k0, q0) : max(k0, q0);
-                k1 = (lower == up1) ? min(k1, q1) : max(k1, q1);
-            }
-        }
-    }
-    srt[lane] = k0;
-    srt[lane + 32] = k1;
-    __syncwarp();
-    // run heads: first entry, or a texel different from the previous entry's
-    const bool h0 = lane < nent && (lane == 0 || (srt[lane - 1] >> 6) != (k0 >> 6));
-    const bool h1 = lane + 32 < nent && ((srt[lane + 31] >> 6) != (k1 >> 6));
-    const uint32_t hb0 = __ballot_sync(0xffffffffu, h0), hb1 = __ballot_sync(0xffffffffu, h1);
-    const int n0 = __popc(hb0), nruns = n0 + __popc(hb1);
-    for (int j = grp; j < nruns; j += 4) {
-        const int start = j < n0 ? __fns(hb0, 0, j + 1) : 32 + __fns(hb1, 0, j - n0 + 1);
-        const int jn = j + 1;
-        const int end = jn >= nruns ? nent : (jn < n0 ? __fns(hb0, 0, jn + 1) : 32 + __fns(hb1, 0, jn - n0 + 1));
-        const uint32_t texel = srt[start] >> 6;                   // index of (y0, x0) across the three planes
-        const int k = texel >= 2u * HW ? 2 : (texel >= (uint32_t)HW ? 1 : 0);
-        float4 acc[4];
-#pragma unroll
-        for (int c = 0; c < 4; ++c) acc[c] = make_float4(0.f, 0.f, 0.f, 0.f);
-        float pa = 0.f;          // lanes 0..3 of the group: corner lane8's probability-plane gradient of the current part
-        int cur_p = -1;
-        const int pix0 = (int)texel - k * HW;
-        for (int e = start; e < end; ++e) {
-            const int r = p0 + (int)(srt[e] & 63u);
-            const float* rw = rec + r * REC;
-            const int w3 = __float_as_int(rw[3]);
-            const int p = w3 & 255, q = (w3 >> 8) - c0;
-            ENARF_DBG_ASSERT(q >= 0 && q < CH && p < sc.P);
-            const float4 w4 = *reinterpret_cast<const float4*>(rw + 4 + 4 * k);
-            const float4 dx = *reinterpret_cast<const float4*>(X + q * DXS + 4 * lane8);
-            fma4(acc[0], w4.x, dx);
-            fma4(acc[1], w4.y, dx);
-            fma4(acc[2], w4.z, dx);
-            fma4(acc[3], w4.w, dx);
-            if (p != cur_p) {      // (uniform across the group) flush the previous part's corner sums
-                if (cur_p >= 0 && lane8 < 4 && pa != 0.f)
-                    atomicAdd(dprob + (size_t)(3 * cur_p + k) * HW + pix0 + (lane8 >> 1) * W + (lane8 & 1), pa);
-                cur_p = p;
-                pa = 0.f;
-            }
-            // d v_k = d w_p * w_p * (1 - sigmoid(v_k)); the checkpointed bilinear weights already carry w_p
-            const float dv = fdot_s[r] * (1.f - rw[17 + k]);
-            const float bw = lane8 == 0 ? w4.x : lane8 == 1 ? w4.y : lane8 == 2 ? w4.z : w4.w;
-            pa = fmaf(bw, dv, pa);
-        }
-        if (lane8 < 4 && pa != 0.f)
-            atomicAdd(dprob + (size_t)(3 * cur_p + k) * HW + pix0 + (lane8 >> 1) * W + (lane8 & 1), pa);
-        float* d0 = dfeat + (size_t)texel * FEAT;
-        red_add_v4(d0, acc[0].x, acc[0].y, acc[0].z, acc[0].w);
-        red_add_v4(d0 + FEAT, acc[1].x, acc[1].y, acc[1].z, acc[1].w);
-        red_add_v4(d0 + (size_t)W * FEAT, acc[2].x, acc[2].y, acc[2].z, acc[2].w);
-        red_add_v4(d0 + (size_t)W * FEAT + FEAT, acc[3].x, acc[3].y, acc[3].z, acc[3].w);
-    }
-}
-
 template <typename T>
 __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
     // bf16 feature planes (parity bar 1e-2): single-pass TF32 GEMMs instead of the error-compensated 3xTF32
@@ -473,10 +365,11 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
     wgrad_zero(wg);
     if (tid < 4) s.db3[tid] = 0.f;
     if (tid == 0) {
-        mbar_init(&s.rec_bar, 1);
+        mbar_init(&s.rec_bar[0], 1);
+        mbar_init(&s.rec_bar[1], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    uint32_t rec_phase = 0;      // parity of the next completion of rec_bar (uniform across the CTA)
+    uint32_t rec_phase = 0, rec_phase1 = 0;   // parities of the next completions of rec_bar[0 / 1] (uniform across the CTA)
     PHASE_DECL;
 
     for (;;) {
@@ -615,7 +508,8 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 }
             }
         };
-        int c1 = n_active > 0 ? chunk_end(s.t, 0) : 0;
+        const int pair_cap = tb >= 0 ? PB + PBX : PB;
+        int c1 = n_active > 0 ? chunk_end(s.t, 0, pair_cap) : 0;
         if (a.feat && n_active > 0) {
             load_rows(0, c1);
             store_rows(c1);
@@ -631,7 +525,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 // GEMM phases run under it); it replaced ~3 16-byte cp.async per thread and their shared-memory wavefronts
                 if (tid == 0)
                     bulk_load(s.r.rec, a.ck.rec + (size_t)(tb + pair0) * REC,
-                              (uint32_t)((s.t.pref[c1] - pair0) * REC * sizeof(float)), &s.rec_bar);
+                              (uint32_t)(min(PB, s.t.pref[c1] - pair0) * REC * sizeof(float)), &s.rec_bar[0]);
             } else {
                 setup_pairs<false>(s.t, s.r.rec, s.part, sc, b, c0, c1, tid);
             }
@@ -744,21 +638,23 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
                 }
             }
             __syncthreads();
+            const bool overflow = tb >= 0 && s.t.pref[c1] - pair0 > PB;
+            if (overflow && tid == 0)   // G1 is dead: its buffer takes the records beyond PB, awaited inside the scatter
+                bulk_load(s.A1, a.ck.rec + (size_t)(tb + pair0 + PB) * REC,
+                          (uint32_t)((s.t.pref[c1] - pair0 - PB) * REC * sizeof(float)), &s.rec_bar[1]);
             if (tb >= 0) {   // this chunk's records have landed (every thread observes the barrier phase itself)
-                mbar_wait(&s.rec_bar, rec_phase);
+                mbar_wait(&s.rec_bar[0], rec_phase);
                 rec_phase ^= 1u;
             }
             PHASE(11);  // dX
-            const int c1n = c1 < n_active ? chunk_end(s.t, c1) : c1;
+            const int c1n = c1 < n_active ? chunk_end(s.t, c1, pair_cap) : c1;
             if (a.feat && c1 < n_active) load_rows(c1, c1n - c1);   // next chunk's rows, in flight during the scatter
-#ifdef ENARF_MERGED_SCATTER
-            if (tb >= 0)     // G1 (in A1) is dead since the dW1 / dX phase: its rows are the merged scatter's scratch
-                scatter_chunk_merged(s.t, s.r.rec, s.A2, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT, s.A1,
-                                     reinterpret_cast<uint32_t*>(s.A1 + PB));
-#else
-            if (tb >= 0) scatter_chunk<T, true>(s.t, s.r.rec, s.A2, a, b, c0, c1, tid, a.ck.feat + (size_t)(tb + pair0) * FEAT);
-#endif
-            else scatter_chunk<T, false>(s.t, s.r.rec, s.A2, a, b, c0, c1, tid, nullptr);
+            if (tb >= 0)
+                scatter_chunk<T, true>(s.t, s.r.rec, s.A1, &s.rec_bar[1], rec_phase1, s.A2, a, b, c0, c1, tid,
+                                       a.ck.feat + (size_t)(tb + pair0) * FEAT);
+            else
+                scatter_chunk<T, false>(s.t, s.r.rec, nullptr, nullptr, 0u, s.A2, a, b, c0, c1, tid, nullptr);
+            if (overflow) rec_phase1 ^= 1u;
             if (a.feat && c1 < n_active) store_rows(c1n - c1);   // X is free since the dW1 / dX phase
             __syncthreads();
             PHASE(12);  // scatter

@@ -305,16 +305,16 @@ __device__ __forceinline__ void tile_points(TileSmem& t, RecSmem& r, const float
     tile_compact(t, rays, g.S, g.S, 0, 1, 0xffffffffu, nullptr, tid);
 }
 
-// End (exclusive) of the chunk starting at active index a: at most CH points and PB pairs.
-__device__ __forceinline__ int chunk_end(const TileSmem& t, int a) {
+// End (exclusive) of the chunk starting at active index a: at most CH points and `cap` pairs (cap >= 32).
+__device__ __forceinline__ int chunk_end(const TileSmem& t, int a, int cap = PB) {
     const int na = t.n_active;
     int e = min(a + CH, na);
     const int p0 = t.pref[a];
-    if (t.pref[e] - p0 > PB) {
-        int lo = a + 1, hi = e;   // invariant: pref[lo]-p0 <= PB (one point has <= 32 pairs), answer in [lo, hi)
+    if (t.pref[e] - p0 > cap) {
+        int lo = a + 1, hi = e;   // invariant: pref[lo]-p0 <= cap (one point has <= 32 pairs), answer in [lo, hi)
         while (hi - lo > 1) {
             const int mid = (lo + hi) >> 1;
-            if (t.pref[mid] - p0 <= PB) lo = mid; else hi = mid;
+            if (t.pref[mid] - p0 <= cap) lo = mid; else hi = mid;
         }
         e = lo;
     }
