@@ -528,7 +528,7 @@ def main():
     sync()
     ms = t0.elapsed_time(t1) / args.steps
     kt = timer.totals()
-    overflow = int((w["ckpt_tile_base"] < 0).sum().item())     # tiles of the last step whose pairs did not fit the checkpoint
+    overflow = int((w["ckpt_tile_base"] == -1).sum().item())     # tiles of the last step whose pairs did not fit the checkpoint
     # ---- end-to-end arm (host buffers in, image + loss out) ----
     gen, host, out_img, out_loss, h2d, d2h = build_e2e(w, device, graph=not args.eager_e2e)
     for _ in range(max(3, args.warmup)):

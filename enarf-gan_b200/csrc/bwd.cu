@@ -384,6 +384,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         const int rays = min(a.rays_per_tile, n - ray0);
         const int tp = rays * S;
         const int tb = (a.ck.rec && a.feat) ? a.ck.tile_base[tile] : -1;   // this tile's slice of the pair checkpoint
+        if (tb == -2) continue;   // the forward found no (point, part) pair in this tile: nothing to differentiate
         if (b != cur_b) {
             if (cur_b >= 0) wgrad_flush(wg, m, s.db3, a, cur_b, tid);
             load_part_params(s.part, sc, b, tid, NT);

@@ -131,6 +131,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
         // ---- chunks of 32 active points, one warp each, no CTA barrier; with early termination on an opaque scene the
         // sample groups go front to back in rounds, each followed by a partial composite that retires finished rays
         int n_done = 0;
+        bool empty_tile = false;
         for (int rd = 0; rd < rounds; ++rd) {
             // (round 0: every ray is alive -- s.t.alive was only just written by thread 0)
             tile_compact(s.t, rays, S, ert ? ERT_GROUP : S, rounds == 1 ? 0 : rd, rounds == 1 ? groups : rd + 1,
@@ -154,7 +155,9 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                     else np_tile = s.t.pref[n_active];
                     // once the checkpoint is full the cursor is left alone, so it cannot wrap however many tiles follow
                     int base = -1;
-                    if (*reinterpret_cast<volatile int*>(a.ck.cursor) <= a.ck.capacity) {
+                    if (np_tile == 0) {
+                        base = -2;      // no pairs at all: the backward skips the tile outright
+                    } else if (*reinterpret_cast<volatile int*>(a.ck.cursor) <= a.ck.capacity) {
                         base = atomicAdd(a.ck.cursor, np_tile);
                         if ((long long)base + np_tile > a.ck.capacity) base = -1;
                     }
@@ -163,6 +166,35 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                     s.t.pad_[1] = base;
                 }
                 __syncthreads();
+            }
+            if (MODE != MODE_QUERY && rounds == 1 && n_active == 0) {
+                // Nothing of the tile lies inside any part (45 % of the bench's tiles): write what the compositing below
+                // would produce from all-zero densities -- the same values bit for bit -- and take the next tile.
+                const int M0 = (MODE == MODE_COARSE) ? S : S - 1;
+                const size_t gray0 = (size_t)b * n + ray0;
+                if (MODE == MODE_COARSE) {
+                    const float w0 = cadd(cmul(cadd(0.f, 0.f), 0.5f), 0.01f);
+                    for (int i = tid; i < rays * S; i += NT) {
+                        a.weights_out[gray0 * S + i] = w0;
+                        if (a.density_out) a.density_out[gray0 * S + i] = 0.f;
+                    }
+                } else {
+                    for (int i = tid; i < rays * M0; i += NT) a.fine_weights[gray0 * M0 + i] = 0.f;
+                    if (a.point_out) {
+                        float4* dst = reinterpret_cast<float4*>(a.point_out) + gray0 * S;
+                        for (int i = tid; i < tp; i += NT) dst[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                    }
+                    if (tid < rays) {
+                        float* c = a.color + (size_t)b * 3 * n + ray0 + tid;
+                        c[0] = a.bg_const;
+                        c[n] = a.bg_const;
+                        c[2 * (size_t)n] = a.bg_const;
+                        a.mask[gray0 + tid] = 0.f;
+                        a.disp[gray0 + tid] = 0.f;
+                    }
+                }
+                empty_tile = true;      // (n_active is CTA-uniform; the loop top synchronises)
+                break;
             }
             WarpSlab& my = s.u.slab[warp];
             const int g = lane >> 2, t4 = lane & 3;
@@ -234,6 +266,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
             }
             n_done = n_active;
         }
+        if (empty_tile) continue;
         if (MODE != MODE_QUERY && a.ert_stats && tid == 0) {
             atomicAdd(a.ert_stats, n_done);
             if (s.t.skipped) atomicAdd(a.ert_stats + 1, s.t.skipped);

@@ -133,7 +133,8 @@ typedef struct {
     float* rec;          /* (capacity, 20): texel offsets, part | active index << 8, 12 weights x part weight,
                             1 / part weight, 3 sigmoids */
     float* feat;         /* (capacity, 32): part-weighted bilinear feature of the pair; 16-byte aligned */
-    int32_t* tile_base;  /* first pair of every tile, -1 if the tile was not checkpointed */
+    int32_t* tile_base;  /* first pair of every tile; -1: the tile was not checkpointed (the backward recomputes it);
+                            -2: the tile has no pair at all (the backward skips it) */
     int32_t* cursor;     /* one int: pairs handed out so far */
     int64_t capacity;    /* pairs */
 } enarf_pair_ckpt_t;

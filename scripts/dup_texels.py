@@ -19,6 +19,7 @@ torch.cuda.synchronize()
 n_pairs = int(pairs.cursor)
 rec = pairs.rec[:n_pairs]
 base = pairs.tile_base.long()
+base = torch.where(base < 0, torch.full_like(base, n_pairs), base)    # -1 not checkpointed / -2 empty tile: sorted last, own no pair
 tiles = base.numel()
 # tile id of every pair: tiles were handed consecutive slices in the order they claimed them
 order = torch.argsort(base)
