@@ -69,12 +69,26 @@ __global__ void __launch_bounds__(128) depth_range_kernel(
     const float dx = cdot3(s_K[0], s_K[1], s_K[2], u0, u1, u2);
     const float dy = cdot3(s_K[3], s_K[4], s_K[5], u0, u1, u2);
     const float dz = cdot3(s_K[6], s_K[7], s_K[8], u0, u1, u2);
+    // Parts whose bounding sphere (radius sqrt 3 of the unit cube, + 2 % for rounding) the ray misses cannot contain a
+    // probe: they are left out of the 32 x P cube tests below (conservative, so the result is bit for bit the same; most
+    // rays miss most of the 24 parts)
+    uint32_t near_parts = 0;
+    {
+        const float inv_dd = 1.f / fmaxf(dx * dx + dy * dy + dz * dz, 1e-30f);
+        for (int p = 0; p < P; ++p) {
+            const float* q = s_pose + p * 12;
+            const float td = q[9] * dx + q[10] * dy + q[11] * dz;
+            const float dist2 = (q[9] * q[9] + q[10] * q[10] + q[11] * q[11]) - td * td * inv_dd;
+            if (dist2 <= 3.f * 1.04f + 1e-3f) near_parts |= 1u << p;
+        }
+    }
     uint32_t hit = 0;  // bit j: probe j lies inside some part cube
-    for (int j = 0; j < N_PROBE; ++j) {
+    for (int j = 0; j < N_PROBE && near_parts; ++j) {
         const float d = probe_depth(near, far, step, j);
         const float x = cmul(dx, d), y = cmul(dy, d), z = cmul(dz, d);
         bool in = false;
-        for (int p = 0; p < P && !in; ++p) {
+        for (uint32_t pm = near_parts; pm && !in; pm &= pm - 1) {
+            const int p = __ffs(pm) - 1;
             const float* q = s_pose + p * 12;
             float e0 = csub(x, q[9]), e1 = csub(y, q[10]), e2 = csub(z, q[11]);
             float l0 = cdot3(q[0], q[3], q[6], e0, e1, e2);
