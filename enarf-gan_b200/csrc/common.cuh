@@ -134,6 +134,53 @@ __device__ __forceinline__ Bilin bilin_setup(float x, float y, int W, int H) {
     return b;
 }
 
+// The same footprint from its two 1-D halves.  The three planes of a pair sample (c0,c1), (c1,c2), (c2,c0): every
+// coordinate is the x of one plane and the y of another, so with square planes three 1-D set-ups serve all three
+// footprints instead of six (identical arithmetic: bilin_setup(x, y, W, H) == bilin_from(lin_setup(x, W), lin_setup(y, H))).
+struct Lin1 {
+    int i0;
+    float w0, w1;
+};
+__device__ __forceinline__ Lin1 lin_setup(float x, int N) {
+    float ix = ((x + 1.f) * N - 1.f) * 0.5f;
+    float fx = floorf(ix);
+    int x0 = (int)fx;
+    float ax = ix - fx;
+    float wx0 = (x0 >= 0 && x0 < N) ? 1.f - ax : 0.f, wx1 = (x0 + 1 >= 0 && x0 + 1 < N) ? ax : 0.f;
+    if (x0 < 0) { wx0 = wx1; wx1 = 0.f; }
+    if (x0 > N - 2) { wx1 = wx0; wx0 = 0.f; }
+    Lin1 l;
+    l.i0 = min(max(x0, 0), N - 2);
+    l.w0 = wx0;
+    l.w1 = wx1;
+    return l;
+}
+__device__ __forceinline__ Bilin bilin_from(const Lin1& lx, const Lin1& ly) {
+    Bilin b;
+    b.x0 = lx.i0;
+    b.y0 = ly.i0;
+    b.w00 = lx.w0 * ly.w0;
+    b.w01 = lx.w1 * ly.w0;
+    b.w10 = lx.w0 * ly.w1;
+    b.w11 = lx.w1 * ly.w1;
+    return b;
+}
+// footprints of the three planes of a pair at canonical coordinates c[0..2]
+__device__ __forceinline__ void bilin_setup3(const float (&c)[3], int W, int H, Bilin (&bl)[3]) {
+    Lin1 lx[3], ly[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) lx[i] = lin_setup(c[i], W);
+    if (W == H) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) ly[i] = lx[i];
+    } else {
+#pragma unroll
+        for (int i = 0; i < 3; ++i) ly[i] = lin_setup(c[i], H);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) bl[k] = bilin_from(lx[k], ly[(k + 1) % 3]);
+}
+
 // scalar (1-channel) bilinear fetch from a row-major H x W plane
 __device__ __forceinline__ float bilin_fetch1(const float* __restrict__ plane, const Bilin& b, int W) {
     const float* r0 = plane + (b.y0 * W + b.x0);

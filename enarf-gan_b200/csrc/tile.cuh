@@ -343,10 +343,10 @@ __device__ __forceinline__ void setup_pairs(const TileSmem& t, float* rec, const
         float c[3];
         part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
         Bilin bl[3];
+        bilin_setup3(c, W, H, bl);
         float sg[3], wp = 1.f;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
             sg[k] = sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
             wp *= sg[k];
         }
@@ -421,6 +421,7 @@ __device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& 
 #ifndef RECW
 #define RECW 48     // pair records per warp sub-batch (one point has at most 32 pairs)
 #endif
+static_assert(RECW <= 64, "the pair-owner bitmap of gather32_warp is 64 bits");
 #define XSW 32      // feature slab row stride; 8-float granules are XOR-swizzled by the row (mlp_mma.cuh xs_col)
 
 #ifndef FWD_PHASE   // render.cu's development-build phase timer
@@ -445,26 +446,33 @@ __device__ __forceinline__ void gather32_warp(const TileSmem& t, float* rec, flo
         const int mine = (lane >= q0 && lane < np) ? t.pref[a + lane + 1] - base : (RECW + 1);
         const int q1 = q0 + __popc(__ballot_sync(0xffffffffu, mine <= RECW));
         const int npairs = t.pref[a + q1] - base;
+        // which point owns pair r: bit s of `starts` is set when a point's pairs begin at record s (every point has at
+        // least one pair, RECW <= 64) -- the owner of r is the number of set bits at or below r, its first record the
+        // highest of them: two warp reductions and a few bit operations instead of a binary search in shared memory
+        unsigned long long starts;
+        {
+            const int st = (lane >= q0 && lane < q1) ? t.pref[a + lane] - base : 64;
+            const uint32_t lo32 = __reduce_or_sync(0xffffffffu, st < 32 ? 1u << st : 0u);
+            const uint32_t hi32 = __reduce_or_sync(0xffffffffu, (st >= 32 && st < 64) ? 1u << (st - 32) : 0u);
+            starts = ((unsigned long long)hi32 << 32) | lo32;
+        }
         // ---- setup: one lane per pair ------------------------------------------------------------------
         for (int r = lane; r < npairs; r += 32) {
             const int target = base + r;
-            int lo = a + q0, hi = a + q1;   // largest q with pref[q] <= target
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (t.pref[mid] <= target) lo = mid; else hi = mid;
-            }
+            const unsigned long long below = starts & (~0ull >> (63 - r));
+            const int lo = a + q0 + __popcll(below) - 1;
             const float4 pm = t.pm[t.list[lo]];
             uint32_t m = __float_as_uint(pm.w);
-            for (int k = target - t.pref[lo]; k > 0; --k) m &= m - 1;
+            for (int k = r - (63 - __clzll(below)); k > 0; --k) m &= m - 1;
             const int p = __ffs(m) - 1;
             ENARF_DBG_ASSERT(p >= 0 && p < sc.P && r < RECW);
             float c[3];
             part_canonical(s_part + p * PART_STRIDE, pm.x, pm.y, pm.z, c[0], c[1], c[2]);
             Bilin bl[3];
+            bilin_setup3(c, W, H, bl);
             float sg[3], wp = 1.f;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
-                bl[k] = bilin_setup(c[k], c[(k + 1) % 3], W, H);
                 ENARF_DBG_ASSERT(bl[k].x0 >= 0 && bl[k].x0 <= W - 2 && bl[k].y0 >= 0 && bl[k].y0 <= H - 2);
                 sg[k] = sigmoidf_(bilin_fetch1(prob + (size_t)(3 * p + k) * H * W, bl[k], W));
                 wp *= sg[k];
