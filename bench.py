@@ -576,16 +576,23 @@ def main():
     (vc, ac), (vf, af) = mean_valid_parts(w)
     R = B * SIZE * SIZE
     # per (point, valid part) 396*s bytes, per ray the streamed I/O
+    survey_bwd = 2 * R * NF * vf * 396 * 4 + R * (20 + NF * 4 + NF * 16)    # re-gather + reductions
+    # what the backward really moves with the forward's checkpoints: per pair its 80-byte record and its
+    # 128-byte feature line in, 12 x 128 B + 12 x 4 B of reductions out; per active point its 128-byte feature row;
+    # per ray the streamed inputs
+    ckpt_bwd = R * NF * vf * (80 + 128 + 396 * 4) + R * NF * af * 128 + R * (20 + NF * 4 + NF * 16)
     alg = {"coarse": R * NC * vc * 396 * 4 + R * (20 + NC * 4),
            "fine_fwd": R * NF * vf * 396 * 4 + R * (20 + NF * 4 + (NF - 1) * 4 + NF * 4 + NF * 16),
-           "fine_bwd": 2 * R * NF * vf * 396 * 4 + R * (20 + NF * 4 + NF * 16)}
+           "fine_bwd": survey_bwd}
     dom = max(alg, key=lambda k: kt[k])
     peak, peak_src = peaks()
     achieved = alg[dom] / (kt[dom] * 1e-3) / 1e9
     roof = {"bound": "l2-atomics + issue (NOT hbm: the planes are L2-resident, see dram_frac)", "kernel": dom,
             "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "peak_source": peak_src,
-            "frac_definition": "SURVEY 8(d) algorithmic gather bytes / kernel time / measured HBM copy peak; these bytes are "
-                               "served by L2, so frac is an L2-gather rate expressed in HBM units, not DRAM utilisation",
+            "frac_definition": "SURVEY 8(d) algorithmic bytes (396*s B per (point, part) pair, the backward counted as re-gather + "
+                               "reductions) / CUDA-event kernel time / measured HBM copy peak.  These bytes are served by L2, so frac "
+                               "is an L2-traffic rate expressed in HBM units, not DRAM utilisation (that is dram_frac); the checkpointed "
+                               "backward no longer re-gathers, so what it really moves is moved_bytes_per_launch / moved_frac",
             "algorithmic_bytes_per_launch": alg[dom], "kernel_ms": kt[dom],
             "mean_valid_parts_per_point": {"coarse": vc, "fine": vf}, "active_point_fraction": {"coarse": ac, "fine": af},
             "kernel_ms_all": kt, "kernel_share_of_step": kt[dom] / ms, "traffic": None}
@@ -598,6 +605,8 @@ def main():
             roof["traffic_source"] = tj["source"]
             roof["dram_frac"] = roof["traffic"] / (kt[dom] * 1e-3) / 1e9 / peak
     if dom == "fine_bwd":
+        roof["moved_bytes_per_launch"] = ckpt_bwd     # 208 B of checkpoint in + 1 584 B of reductions out per pair, 128 B per point
+        roof["moved_frac"] = ckpt_bwd / (kt[dom] * 1e-3) / 1e9 / peak
         # the floor the backward cannot go under: its reductions at the measured L2-resident rates
         # (scripts/microbench/red_rate.cu, profiles/red_rate_r1.txt): 12 x 8 lane-level red.v4 per pair at 381.5 G/s and
         # 12 scattered 4-byte reductions per pair at 195.6 G/s
