@@ -117,3 +117,26 @@ def test_more_than_32_parts_is_refused():
                                (torch.zeros(B, 4, 64, device="cuda"), torch.zeros(4, device="cuda"))])
         d = torch.ones(B, 8, device="cuda")
         ops.render_coarse(gs, d, d * 2, torch.ones(B, 3, 8, device="cuda"), 48)
+
+
+def test_large_point_query_is_tiling_invariant_and_repeatable(b2):
+    """Regression test for the tile_compact race fixed in round 2 (a warp that entered the compaction late could read
+    an already advanced list length: corrupt active list -> wrong densities / a faulting texel offset, seen only at
+    large point counts).  The point query over 2 x 2^19 points must give bit-identical masks and densities on every
+    repetition and whatever the tiling (one call vs sixteen slices: a point's result depends on that point only)."""
+    from enarf_gan_b200 import ops
+    gs = b2["gs"]
+    B, N = b2["cfg"]["B"], 1 << 19
+    g = torch.Generator().manual_seed(77)
+    centre = gs.pose[:, :, :3, 3].mean(dim=1)                                   # (B,3): the body's centre in camera space
+    pts = (centre[:, :, None].cpu() + 1.2 * torch.randn(B, 3, N, generator=g)).cuda().contiguous()
+    den0, _, m0 = ops.density_query(gs, pts, want_color=False, want_mask=True)
+    assert (m0 != 0).float().mean().item() > 0.05, "the cloud must hit the parts"
+    for _ in range(5):
+        den, _, m = ops.density_query(gs, pts, want_color=False, want_mask=True)
+        assert torch.equal(m, m0) and torch.equal(den, den0)
+    step = N // 16
+    for k in range(16):
+        sl = pts[:, :, k * step:(k + 1) * step].contiguous()
+        den, _, m = ops.density_query(gs, sl, want_color=False, want_mask=True)
+        assert torch.equal(m, m0[:, k * step:(k + 1) * step]) and torch.equal(den, den0[:, :, k * step:(k + 1) * step])
