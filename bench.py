@@ -182,7 +182,7 @@ def step_device(w, step_idx, timer=None, world=None):
     wb = timed("coarse", lambda: ops.render_coarse(scene, dmin, dmax, direction, NC))
     bins = timed("fine_sample", lambda: ops.fine_sample(wb, NF, seed=step_idx))
     color, mask, disp, fw, fd, pts, feat, pairs = timed("fine_fwd", lambda: ops._render_fine_fwd(
-        scene, dmin, dmax, direction, bins, want_points=True, want_feat=True, want_pairs=True))
+        scene, dmin, dmax, direction, bins, want_points=True, want_feat=True, want_pairs=True, skip_last=True))   # as a training step
     d_tp = torch.empty_like(w["tri_plane"])     # as ops.RenderFine.backward: feature channels are stored by unpack
     for b in range(B):                          # per sample: contiguous slices -> vectorised fills
         d_tp[b, 96:].zero_()

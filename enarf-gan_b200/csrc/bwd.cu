@@ -412,7 +412,7 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         // With the forward's pair checkpoint the active list must be the forward's own (which evaluates the last sample of
         // a ray too); that sample then flows through with a zero upstream gradient.  Otherwise it is skipped outright.
         TileGeom geom = a.g;
-        geom.skip_last = tb < 0;
+        geom.skip_last = tb < 0 || a.ck.skip_last;      // (the forward's own list when it left the last samples out)
         tile_masks<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
         {
             // the forward's list: point order, or with early termination group-major without the samples it dropped

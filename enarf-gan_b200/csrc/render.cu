@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
                         for (int h = 0; h < 2; ++h) {
                             const int row = 16 * mt + 8 * h + g;
                             if (row < np) {
-                                const float v0 = lrelu_s2(o3[mt][2 * h]), v1 = lrelu_s2(o3[mt][2 * h + 1]);
+                                const float v0 = lrelu_folded(o3[mt][2 * h]), v1 = lrelu_folded(o3[mt][2 * h + 1]);
                                 const float2 r = t4 == 0 ? make_float2(tanhf(v0), tanhf(v1))
                                                          : make_float2(tanhf(v0), fmaxf(v1, 0.f) * 10.f);
                                 reinterpret_cast<float2*>(&out[s.t.list[a0 + row]])[t4] = r;
@@ -483,6 +483,7 @@ extern "C" int enarf_render_fine_fwd(const enarf_scene_t* scene, const float* de
                           ((uintptr_t)pair_ckpt->rec & 15) == 0 && ((uintptr_t)pair_ckpt->feat & 15) == 0,
                       ENARF_ERR_INVALID_ARG, "enarf_render_fine_fwd: incomplete or misaligned pair checkpoint");
         a.ck = *pair_ckpt;
+        a.g.skip_last = pair_ckpt->skip_last ? 1 : 0;
     }
     return launch_render<MODE_FINE>(a, "enarf_render_fine_fwd", (cudaStream_t)stream);
 }

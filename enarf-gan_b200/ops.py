@@ -226,15 +226,16 @@ PAIR_CKPT_MAX = 48 << 20      # pairs (208 B each)
 class PairCheckpoint:
     """Caller-owned buffers of enarf_pair_ckpt_t (include/enarf_b200.h) for one fine pass."""
 
-    def __init__(self, B, n, Nf, device):
+    def __init__(self, B, n, Nf, device, skip_last=False):
         tiles = lib().enarf_fine_tiles_per_sample(n, Nf)
+        self.skip_last = bool(skip_last)
         self.capacity = int(max(1, min(PAIR_CKPT_MAX, PAIR_CKPT_PER_POINT * B * n * Nf)))
         self.rec = torch.empty(self.capacity, 20, device=device)
         self.feat = torch.empty(self.capacity, FEAT_DIM, device=device)
         self.tile_base = torch.empty(max(1, B * tiles), device=device, dtype=torch.int32)
         self.cursor = torch.zeros(1, device=device, dtype=torch.int32)
         self.c = _abi.PairCkpt(self.rec.data_ptr(), self.feat.data_ptr(), self.tile_base.data_ptr(),
-                               self.cursor.data_ptr(), self.capacity)
+                               self.cursor.data_ptr(), self.capacity, int(self.skip_last), 0)
 
     @property
     def ref(self):
@@ -244,15 +245,17 @@ class PairCheckpoint:
         return self.rec, self.feat, self.tile_base, self.cursor
 
     @classmethod
-    def from_tensors(cls, rec, feat, tile_base, cursor):
+    def from_tensors(cls, rec, feat, tile_base, cursor, skip_last=False):
         self = cls.__new__(cls)
         self.rec, self.feat, self.tile_base, self.cursor, self.capacity = rec, feat, tile_base, cursor, rec.shape[0]
-        self.c = _abi.PairCkpt(rec.data_ptr(), feat.data_ptr(), tile_base.data_ptr(), cursor.data_ptr(), self.capacity)
+        self.skip_last = bool(skip_last)
+        self.c = _abi.PairCkpt(rec.data_ptr(), feat.data_ptr(), tile_base.data_ptr(), cursor.data_ptr(), self.capacity,
+                               int(self.skip_last), 0)
         return self
 
 
 def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want_feat=False, want_pairs=False,
-                     ert_eps=0.0, ert_hint=None, ert_stats=None, bg_const=0.0):
+                     ert_eps=0.0, ert_hint=None, ert_stats=None, bg_const=0.0, skip_last=False):
     """-> color, mask, disp, fine_weights, fine_depth [, points (B,n,Nf,4)] [, feat (B,n,Nf,32) checkpoint: only
     the rows of samples inside a part are written] [, PairCheckpoint]."""
     B, n, Nf = bins.shape
@@ -264,7 +267,9 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
     fd = torch.empty(B, n, Nf, device=dev)
     pts = torch.empty(B, n, Nf, 4, device=dev) if (want_points or ert_eps > 0) else None
     feat = torch.empty(B, n, Nf, FEAT_DIM, device=dev) if want_feat else None
-    pairs = PairCheckpoint(B, n, Nf, dev) if want_pairs else None
+    # skip_last (with the pair checkpoint only): the last sample of every ray -- evaluated and then dropped by the
+    # reference, rendering.py:306-308 -- is left out; its row of `points` is 0
+    pairs = PairCheckpoint(B, n, Nf, dev, skip_last=skip_last) if want_pairs else None
     check(lib().enarf_render_fine_fwd(scene.ref, ptr(dmin), ptr(dmax), ptr(direction), ptr(bins), n, Nf, ptr(color),
                                       ptr(mask), ptr(disp), ptr(fw), ptr(fd), ptr(pts, allow_none=True),
                                       ptr(feat, allow_none=True), pairs.ref if pairs else None, float(ert_eps),
@@ -282,11 +287,14 @@ def _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=False, want
 
 def _fine_forward(ctx, scene, dmin, dmax, direction, bins, ert):
     """Forward of both autograd Functions: run the fused pass with the checkpoints a backward wants and stash them.
-    ``ert`` = (ert_eps, ert_hint, ert_stats[, bg_const]): early ray termination and the constant background."""
+    ``ert`` = (ert_eps, ert_hint, ert_stats[, bg_const[, lean]]): early ray termination, the constant background, and
+    ``lean`` = the caller does not read the per-sample outputs (training): the last sample of every ray is not evaluated."""
     pairs_on = SAVE_FEATURES and PAIR_CKPT
+    lean = bool(ert[4]) if len(ert) > 4 else False
     out = _render_fine_fwd(scene, dmin, dmax, direction, bins, want_points=True, want_feat=SAVE_FEATURES,
                            want_pairs=pairs_on, ert_eps=ert[0], ert_hint=ert[1], ert_stats=ert[2],
-                           bg_const=ert[3] if len(ert) > 3 else 0.0)
+                           bg_const=ert[3] if len(ert) > 3 else 0.0, skip_last=lean and pairs_on)
+    ctx.skip_last = lean and pairs_on
     ctx.scene = scene
     ctx.ert_eps = float(ert[0])
     ctx.bg_const = float(ert[3]) if len(ert) > 3 else 0.0
@@ -308,7 +316,7 @@ def _fine_backward(ctx, grads, d_feat, d_prob, d_prob_stride):
     scene = ctx.scene
     dmin, dmax, direction, bins, pts, *rest = ctx.saved_tensors
     feat = rest.pop(0) if ctx.has_feat else None
-    pairs = PairCheckpoint.from_tensors(*rest) if ctx.has_pairs else None
+    pairs = PairCheckpoint.from_tensors(*rest, skip_last=ctx.skip_last) if ctx.has_pairs else None
     _, n, Nf = bins.shape
     g = [None if t is None else t.contiguous().float() for t in grads]
     dw = [torch.zeros_like(w) for w in scene.w]
@@ -402,12 +410,13 @@ def render_fine(scene, dmin, dmax, direction, bins, tri_plane=None, decoder=None
         return out if want_points is None or want_points else out + (None,)
     (w1, b1), (w2, b2), (w3, b3) = decoder
     scene.b_shapes = [b1.shape, b2.shape, b3.shape]
+    lean = not want_points        # nobody reads the per-sample outputs: the rays' last samples need not be evaluated
     if isinstance(tri_plane, (tuple, list)):        # (feat_planes channels-last, prob_planes NCHW)
         out = RenderFinePlanes.apply(scene, dmin, dmax, direction, bins, tri_plane[0], tri_plane[1], w1, w2, w3, b1, b2, b3,
-                                     (ert_eps, ert_hint, ert_stats, bg_const))
+                                     (ert_eps, ert_hint, ert_stats, bg_const, lean))
         return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
     out = RenderFine.apply(scene, dmin, dmax, direction, bins, tri_plane, w1, w2, w3, b1, b2, b3,
-                           (ert_eps, ert_hint, ert_stats, bg_const))
+                           (ert_eps, ert_hint, ert_stats, bg_const, lean))
     return out[:5] if want_points is None else (out if want_points else out[:5] + (None,))
 
 

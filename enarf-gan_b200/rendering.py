@@ -148,7 +148,10 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
                       idx=getattr(model, "rng_given", (None, None))[0],
                       jitter=getattr(model, "rng_given", (None, None))[1],
                       tri_plane=tri_plane if track else None, decoder=decoder if track else None,
-                      return_intermediate=return_intermediate or not model.training, want_points=True,
+                      return_intermediate=return_intermediate or not model.training,
+                      # per-sample outputs only where somebody reads them (evaluation, return_intermediate): a training
+                      # step then skips the rays' last samples, whose density the reference computes and drops
+                      want_points=return_intermediate or not model.training,
                       ert_eps=float(getattr(model, "ert_eps", 0.0)), ert_prev=getattr(model, "_ert_prev", None),
                       bg_const=float(getattr(model, "_bg_const", 0.0)))
     if "ert_stats" in out:
@@ -163,7 +166,9 @@ def render(model, image_coord, pose_to_camera, inv_intrinsics, render_scale: flo
         n = out["fine_weights"].shape[1]
         model.buffers_tensors["fine_weights"] = out["fine_weights"][:, None]
         model.buffers_tensors["fine_depth"] = out["fine_depth"][:, None]
-        model.buffers_tensors["fine_density"] = out["points"][..., 3].reshape(B, 1, n * Nf)
+        # (a training step without return_intermediate does not materialise the per-sample densities: None)
+        model.buffers_tensors["fine_density"] = (out["points"][..., 3].reshape(B, 1, n * Nf) if out["points"] is not None
+                                                 else None)
         if not model.training:
             model.temporal_state.update(fine_depth=out["fine_depth"][:, None],
                                         fine_density=out["points"][..., :-1, 3][:, None],

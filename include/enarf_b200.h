@@ -137,6 +137,11 @@ typedef struct {
                             -2: the tile has no pair at all (the backward skips it) */
     int32_t* cursor;     /* one int: pairs handed out so far */
     int64_t capacity;    /* pairs */
+    int32_t skip_last;   /* != 0: the forward leaves out the LAST sample of every ray.  That sample only closes the last
+                            interval: the reference evaluates it and then drops its density and colour
+                            (rendering.py:306-308, [..., :Np-1]), so no rendered output or gradient depends on it; its
+                            point_out entry is then 0.  For callers that do not read the per-sample outputs (training). */
+    int32_t reserved;
 } enarf_pair_ckpt_t;
 int enarf_fine_tiles_per_sample(int n, int Nf);
 
