@@ -28,7 +28,7 @@ class Scene(ctypes.Structure):
 class PairCkpt(ctypes.Structure):
     """Mirror of enarf_pair_ckpt_t."""
     _fields_ = [("rec", c_void_p), ("feat", c_void_p), ("tile_base", c_void_p), ("cursor", c_void_p),
-                ("capacity", c_int64), ("skip_last", c_int32), ("reserved", c_int32)]
+                ("capacity", c_int64), ("skip_last", c_int32), ("reserved", c_int32), ("count", c_void_p)]
 
 
 _P = c_void_p

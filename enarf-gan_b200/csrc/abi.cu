@@ -14,7 +14,7 @@ void enarf_set_error(const char* fmt, ...) {
 }
 
 extern "C" const char* enarf_last_error(void) { return g_err; }
-extern "C" int enarf_version(void) { return 152; }
+extern "C" int enarf_version(void) { return 153; }
 
 // SM count of the CURRENT device (the one the caller's pointers live on), cached per device id: a process that
 // drives several GPUs gets each one's own grid size.  Benign race: concurrent first calls store the same value.

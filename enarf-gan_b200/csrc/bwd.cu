@@ -120,6 +120,39 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t pari
         "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(b), "r"(parity) : "memory");
 }
 
+// The tile's depths and active set from the forward's per-sample part counts instead of the 24-part geometry (checkpointed
+// tiles only: their pair records already hold everything else).  A sample with c valid parts gets the stand-in mask
+// (1 << c) - 1: tile_compact only looks at its population count.  Ends synchronised, like tile_masks.
+__device__ __forceinline__ void tile_from_counts(TileSmem& t, const TileGeom& g, const uint8_t* __restrict__ count, int b,
+                                                 int ray0, int rays, int tid) {
+    const int lane = tid & 31;
+    const int S = g.S, n = g.n, tp = rays * S;
+    if (tid == 0) {
+        t.n_active = 0;
+        t.skipped = 0;
+    }
+    if (tid < rays) {
+        const size_t o = (size_t)b * n + ray0 + tid;
+        t.ray[tid * 8 + 0] = g.dmin[o];
+        t.ray[tid * 8 + 1] = g.dmax[o];
+    }
+    __syncthreads();
+    const size_t p0 = ((size_t)b * n + ray0) * S;
+    for (int i = tid; i < ((tp + 31) & ~31); i += NT) {
+        uint32_t m = 0;
+        if (i < tp) {
+            const int rr = i / S, j = i - rr * S;
+            t.depth[rr * (S + 1) + j] = clerp(t.ray[rr * 8], t.ray[rr * 8 + 1], g.bins[p0 + i]);
+            const uint32_t c = count[p0 + i];
+            m = c >= 32u ? 0xffffffffu : (1u << c) - 1u;
+            t.pm[i] = make_float4(0.f, 0.f, 0.f, __uint_as_float(m));
+        }
+        const uint32_t bal = __ballot_sync(0xffffffffu, m != 0);
+        if (lane == 0) t.act[i >> 5] = bal;
+    }
+    __syncthreads();
+}
+
 __device__ __forceinline__ float act_grad(float a) { return (a > 0.f ? 1.f : 0.2f) * 1.4142135623730951f; }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -413,7 +446,8 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         // a ray too); that sample then flows through with a zero upstream gradient.  Otherwise it is skipped outright.
         TileGeom geom = a.g;
         geom.skip_last = tb < 0 || a.ck.skip_last;      // (the forward's own list when it left the last samples out)
-        tile_masks<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
+        if (tb >= 0 && a.ck.count) tile_from_counts(s.t, geom, a.ck.count, b, ray0, rays, tid);
+        else tile_masks<TILE_FINE>(s.t, s.r, s.part, geom, sc.P, b, ray0, rays, tid);
         {
             // the forward's list: point order, or with early termination group-major without the samples it dropped
             const bool ert = a.ert_eps > 0.f;

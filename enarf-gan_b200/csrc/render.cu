@@ -125,6 +125,9 @@ __global__ void __launch_bounds__(NT, 2) render_kernel(const RenderArgs a) {
         if (ert && tid < MAX_RAYS) s.t.carry[tid] = 0.f;
         if (MODE == MODE_QUERY && a.q_mask)
             for (int i = tid; i < tp; i += NT) a.q_mask[(size_t)b * n + ray0 + i] = __float_as_uint(s.t.pm[i].w);
+        if (MODE == MODE_FINE && a.ck.rec && a.ck.count)   // valid parts per sample: the backward's shortcut to this tile's list
+            for (int i = tid; i < tp; i += NT)
+                a.ck.count[((size_t)b * n + ray0) * S + i] = (uint8_t)__popc(__float_as_uint(s.t.pm[i].w));
         float4* out = s.t.pm;
 
         FWD_PHASE(0);   // tile prologue: rays, phase 0/1, compaction, prefix

@@ -234,23 +234,25 @@ class PairCheckpoint:
         self.feat = torch.empty(self.capacity, FEAT_DIM, device=device)
         self.tile_base = torch.empty(max(1, B * tiles), device=device, dtype=torch.int32)
         self.cursor = torch.zeros(1, device=device, dtype=torch.int32)
+        self.count = torch.empty(B, n, Nf, device=device, dtype=torch.uint8)     # valid parts per sample
         self.c = _abi.PairCkpt(self.rec.data_ptr(), self.feat.data_ptr(), self.tile_base.data_ptr(),
-                               self.cursor.data_ptr(), self.capacity, int(self.skip_last), 0)
+                               self.cursor.data_ptr(), self.capacity, int(self.skip_last), 0, self.count.data_ptr())
 
     @property
     def ref(self):
         return ctypes.byref(self.c)
 
     def tensors(self):
-        return self.rec, self.feat, self.tile_base, self.cursor
+        return self.rec, self.feat, self.tile_base, self.cursor, self.count
 
     @classmethod
-    def from_tensors(cls, rec, feat, tile_base, cursor, skip_last=False):
+    def from_tensors(cls, rec, feat, tile_base, cursor, count, skip_last=False):
         self = cls.__new__(cls)
         self.rec, self.feat, self.tile_base, self.cursor, self.capacity = rec, feat, tile_base, cursor, rec.shape[0]
+        self.count = count
         self.skip_last = bool(skip_last)
         self.c = _abi.PairCkpt(rec.data_ptr(), feat.data_ptr(), tile_base.data_ptr(), cursor.data_ptr(), self.capacity,
-                               int(self.skip_last), 0)
+                               int(self.skip_last), 0, count.data_ptr())
         return self
 
 

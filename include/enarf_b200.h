@@ -142,6 +142,9 @@ typedef struct {
                             (rendering.py:306-308, [..., :Np-1]), so no rendered output or gradient depends on it; its
                             point_out entry is then 0.  For callers that do not read the per-sample outputs (training). */
     int32_t reserved;
+    uint8_t* count;      /* optional (NULL to skip), (B,n,Nf): number of valid parts of every sample, written by the
+                            forward; with it the backward rebuilds a checkpointed tile's active list without redoing
+                            the 24-part geometry */
 } enarf_pair_ckpt_t;
 int enarf_fine_tiles_per_sample(int n, int Nf);
 
