@@ -574,27 +574,31 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             if (tile_on) decoder_layer<FEAT, FAST>(s.X, s.dec.w1, W1S, s.dec.b1, s.A1, m);
             __syncthreads();
             PHASE(4);   // L1
+            // Head backward from the forward's own outputs (four lanes per point, lane c owns output c): the saved
+            // y = tanh(lrelu(o)) gives tanh' = 1 - y^2 and the sign of o (LeakyReLU and tanh keep it); the saved
+            // sigma = 10 relu(lrelu(o)) is positive exactly when o is.  The head is therefore not evaluated again (it was
+            // 6 % of this kernel: 64 x 4 multiply-adds per point through shared memory and two shuffles).  The value is
+            // requested here, ahead of layer 2, and used after it.
+            float y_saved = 0.f;
+            if (8 * warp < cend && (tid >> 2) < cnt)
+                y_saved = __ldg(a.saved + (((size_t)b * n + ray0) * S + s.t.list[c0 + (tid >> 2)]) * 4 + (tid & 3));
             if (tile_on) decoder_layer<HID, FAST>(s.A1, s.dec.w2, W2S, s.dec.b2, s.A2, m);
             __syncthreads();
             PHASE(5);   // L2
-            if (8 * warp < cend) {   // head forward + backward: four lanes per point, lane c owns output c
+            if (8 * warp < cend) {
                 const int pt = tid >> 2, c = tid & 3;
-                float o3[4];
-                head_split4(s.A2, s.dec, pt, c, o3);
                 float g3 = 0.f;
                 if (pt < cnt) {
                     const float4 gin = s.pg[s.t.list[c0 + pt]];
-                    const float oc = c == 0 ? o3[0] : c == 1 ? o3[1] : c == 2 ? o3[2] : o3[3];
+                    const float ag = (y_saved > 0.f ? 1.f : 0.2f) * 1.4142135623730951f;    // act_grad(o): sign(o) = sign(y)
                     if (c < 3) {   // rgb = tanh(lrelu(o3))
-                        const float y = tanhf(lrelu_s2(oc));
                         const float gc = c == 0 ? gin.x : c == 1 ? gin.y : gin.z;
-                        g3 = gc * (1.f - y * y) * act_grad(oc);
+                        g3 = gc * (1.f - y_saved * y_saved) * ag;
                     } else {       // sigma = 10 * MyReLU(lrelu(o3[3]))
-                        const float raw = lrelu_s2(oc);
                         const float go = 10.f * gin.w;
-                        // MyReLU backward (NeRF/activation.py:12-16): g*[x>=0] + 0.1*g*[x<0]*[g<0]
-                        const float graw = (raw >= 0.f) ? go : (go < 0.f ? 0.1f * go : 0.f);
-                        g3 = graw * act_grad(oc);
+                        // MyReLU backward (NeRF/activation.py:12-16): g*[x>=0] + 0.1*g*[x<0]*[g<0]; x > 0 <=> sigma > 0
+                        const float graw = (y_saved > 0.f) ? go : (go < 0.f ? 0.1f * go : 0.f);
+                        g3 = graw * ag;
                     }
                 }
                 s.G3[c * AS + pt] = g3;

@@ -54,7 +54,6 @@ struct __align__(16) DecoderSmem {
     float w3[4 * W2S];     // [c][o]
     float b1[HID], b2[HID], b3[4];
     float pad_[12];
-    float w3t[HID * 4];    // [o][c]: all four head weights of one hidden unit in one 128-bit load
 };
 
 struct __align__(16) TileSmem {
@@ -97,7 +96,6 @@ __device__ __forceinline__ void load_decoder_smem(DecoderSmem& d, const enarf_sc
     for (int e = tid; e < HID * HID; e += NT) d.w2[(e / HID) * W2S + (e % HID)] = w2[e];
     for (int e = tid; e < 4 * HID; e += NT) {
         d.w3[(e / HID) * W2S + (e % HID)] = w3[e];
-        d.w3t[(e % HID) * 4 + e / HID] = w3[e];
     }
     if (tid < HID) {
         d.b1[tid] = sc.b1[tid];
@@ -389,30 +387,6 @@ __device__ __forceinline__ void gather_chunk(const TileSmem& t, const float* rec
     for (int i = tid; i < FEAT * (cend - cnt); i += nthr) {
         const int row = i / (cend - cnt), col = cnt + i - row * (cend - cnt);
         X[row * AS + col] = 0.f;
-    }
-}
-
-// Decoder head (64 -> 4) with four lanes per point: lane kq sums the hidden units kq, kq+4, ...; after two
-// shuffles every one of the four lanes holds o3[c] = sum_k A2[k][pt] W3[c][k] + b3[c].  All 32 lanes of the
-// warp must call it (points 8*warp .. 8*warp+7).
-__device__ __forceinline__ void head_split4(const float* A2, const DecoderSmem& d, int pt, int kq, float (&o3)[4]) {
-#pragma unroll
-    for (int c = 0; c < 4; ++c) o3[c] = 0.f;
-#pragma unroll 4
-    for (int i = 0; i < HID / 4; ++i) {
-        const int k = kq + 4 * i;
-        const float x = A2[k * AS + pt];
-        const float4 w = *reinterpret_cast<const float4*>(d.w3t + k * 4);
-        o3[0] = fmaf(x, w.x, o3[0]);
-        o3[1] = fmaf(x, w.y, o3[1]);
-        o3[2] = fmaf(x, w.z, o3[2]);
-        o3[3] = fmaf(x, w.w, o3[3]);
-    }
-#pragma unroll
-    for (int c = 0; c < 4; ++c) {
-        o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 1);
-        o3[c] += __shfl_xor_sync(0xffffffffu, o3[c], 2);
-        o3[c] += d.b3[c];
     }
 }
 
