@@ -457,6 +457,39 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
         const int n_active = s.t.n_active;
         PHASE(1);   // tile_points
 
+        // ---- 3. per chunk: records -> gather -> decoder forward -> decoder backward -> scatter -------
+        // Features checkpointed by the forward: 8 lanes per point, one 128-B row each.  A chunk's rows are loaded into
+        // registers one chunk ahead (before the previous chunk's scatter) and stored to shared memory at its start.
+        static_assert(CH == 2 * (NT / 8), "two checkpoint rows per 8-lane group");
+        float4 fx[2];
+        const int l8 = tid & 7;
+        const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
+        auto load_rows = [&](int first, int count) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int q = (tid >> 3) + i * (NT / 8);
+                fx[i] = q < count ? __ldg(fi + (size_t)s.t.list[first + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+        };
+        auto store_rows = [&](int count) {   // fx -> X[channel][point], columns up to the next multiple of 32 zero-filled
+            const int cend_ = (count + 31) & ~31;
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int q = (tid >> 3) + i * (NT / 8);
+                if (q < cend_) {
+                    float* dst = s.X + (l8 * 4) * AS + q;
+                    dst[0] = fx[i].x;
+                    dst[AS] = fx[i].y;
+                    dst[2 * AS] = fx[i].z;
+                    dst[3 * AS] = fx[i].w;
+                }
+            }
+        };
+        const int pair_cap = tb >= 0 ? PB + PBX : PB;
+        int c1 = n_active > 0 ? chunk_end(s.t, 0, pair_cap) : 0;
+        // the first chunk's rows are requested now and stored after the compositing backward, which runs under the loads
+        if (a.feat && n_active > 0) load_rows(0, c1);
+
         // ---- 2. compositing backward, one warp per ray, in place on pg ------------------------------
         float* pgf = reinterpret_cast<float*>(s.pg);
         for (int r = warp; r < rays; r += NWARP) {
@@ -512,44 +545,9 @@ __global__ void __launch_bounds__(NT, 2) render_bwd_kernel(const BwdArgs a) {
             }
             if (lane == 0) *reinterpret_cast<float4*>(go + M * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        __syncthreads();
         PHASE(2);   // composite backward
-
-        // ---- 3. per chunk: records -> gather -> decoder forward -> decoder backward -> scatter -------
-        // Features checkpointed by the forward: 8 lanes per point, one 128-B row each.  A chunk's rows are loaded into
-        // registers one chunk ahead (before the previous chunk's scatter) and stored to shared memory at its start.
-        static_assert(CH == 2 * (NT / 8), "two checkpoint rows per 8-lane group");
-        float4 fx[2];
-        const int l8 = tid & 7;
-        const float4* fi = reinterpret_cast<const float4*>(a.feat) + ((size_t)b * n + ray0) * S * (FEAT / 4);
-        auto load_rows = [&](int first, int count) {
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int q = (tid >> 3) + i * (NT / 8);
-                fx[i] = q < count ? __ldg(fi + (size_t)s.t.list[first + q] * (FEAT / 4) + l8) : make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-        };
-        auto store_rows = [&](int count) {   // fx -> X[channel][point], columns up to the next multiple of 32 zero-filled
-            const int cend_ = (count + 31) & ~31;
-#pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int q = (tid >> 3) + i * (NT / 8);
-                if (q < cend_) {
-                    float* dst = s.X + (l8 * 4) * AS + q;
-                    dst[0] = fx[i].x;
-                    dst[AS] = fx[i].y;
-                    dst[2 * AS] = fx[i].z;
-                    dst[3 * AS] = fx[i].w;
-                }
-            }
-        };
-        const int pair_cap = tb >= 0 ? PB + PBX : PB;
-        int c1 = n_active > 0 ? chunk_end(s.t, 0, pair_cap) : 0;
-        if (a.feat && n_active > 0) {
-            load_rows(0, c1);
-            store_rows(c1);
-        }
-        __syncthreads();
+        if (a.feat && n_active > 0) store_rows(c1);
+        __syncthreads();   // pg (the head's input) and X are complete
         for (int c0 = 0; c0 < n_active;) {
             const int cnt = c1 - c0;
             const int cend = (cnt + 31) & ~31;
